@@ -1,0 +1,153 @@
+/* include/sdpm.h -- C ABI of the B200-native semi-dense probability-mapping path.
+ *
+ * Drop-in boundary for the hot path of atlas-jj/ORB-SLAM-free-space-carving:
+ *   reference class   include/Modeler/ProbabilityMapping.h:61-105   ("PM.h")
+ *   reference code    src/Modeler/ProbabilityMapping.cc              ("PM.cc")
+ *
+ * The reference has no FFI for this path (it is a C++ class that nothing calls); these
+ * entry points are what a maintainer's binding would call from the C++ `ProbabilityMapping`
+ * methods (see INTEGRATION.md and orb-slam-free-space-carving_b200/host/ProbabilityMapping.h).
+ * Plain pointers and sizes only; no CUDA, torch or OpenCV types.  All functions return an
+ * `int` status (0 = SD_OK, negative = SdStatus); the reference's `void` methods silently
+ * `return`/`continue` on bad input (PM.cc:141-142, 160, 393, 408) -- here bad arguments are errors.
+ *
+ * One sd_ctx per GPU.  A context is not thread-safe; several contexts may be driven from
+ * several host threads.  Work is enqueued asynchronously on the context's CUDA streams;
+ * sd_download / sd_sync wait for it.  There is NO CPU fallback: sd_create fails if no CUDA
+ * device is usable.
+ */
+#ifndef SDPM_H
+#define SDPM_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SD_MAX_NEIGHBOURS 40 /* BASELINE.json config 5 sweeps 5..40 covisible neighbours; PM.h:38 covisN = 7 */
+
+typedef enum SdStatus {
+    SD_OK = 0,
+    SD_ERR_INVALID_ARG = -1,
+    SD_ERR_UNKNOWN_KEYFRAME = -2,
+    SD_ERR_NOT_READY = -3, /* stage prerequisites missing (e.g. neighbour without semi-dense maps) */
+    SD_ERR_CUDA = -4,
+    SD_ERR_NO_DEVICE = -5,
+    SD_ERR_SHAPE = -6 /* key frame size differs from the context's */
+} SdStatus;
+
+/* Run-time copy of the compile-time tunables PM.h:38-49 and of the literals in PM.cc. */
+typedef struct SdParams {
+    float lambdaG;     /* PM.h:40 = 8    gradient-magnitude gate (PM.cc:201, 411, 562)            */
+    float lambdaL;     /* PM.h:41 = 80   gradient vs epipolar-line angle, degrees (PM.cc:421)     */
+    float lambdaTheta; /* PM.h:42 = 45   gradient-orientation difference, degrees (PM.cc:431)     */
+    int lambdaN;       /* PM.h:43 = 3    min compatible hypotheses / neighbours (PM.cc:221,623,762) */
+    double theta;      /* PM.h:47 = 0.23 THETA (double literal, PM.cc:436, 455-456)               */
+    double chi2_fuse;  /* 5.99, PM.cc:917, 923                                                    */
+    double chi2_inter; /* 3.84, PM.cc:710                                                         */
+    float slope_limit; /* 4,    PM.cc:393                                                         */
+    int border;        /* 2,    PM.cc:198-199                                                     */
+} SdParams;
+
+/* Device-resident planes of one key frame (for a GPU consumer such as a device-side CARV feed).
+ * Float planes have `pitch_f32` elements per row, the u8 image `pitch_u8` bytes per row. */
+typedef struct SdDevicePlanes {
+    int width, height, pitch_f32, pitch_u8;
+    const uint8_t* gray;        /* KeyFrame::im_                                  */
+    const float* grad;          /* KeyFrame::GradImg                              */
+    const float* theta;         /* KeyFrame::GradTheta (degrees)                  */
+    const float* depth;         /* KeyFrame::depth_map_ after the intra-KF stage  */
+    const float* sigma;         /* KeyFrame::depth_sigma_                         */
+    const float* depth_checked; /* depth_map_ after InterKeyFrameDepthChecking    */
+    const float* points;        /* KeyFrame::SemiDensePointSets_, H x 3W floats   */
+} SdDevicePlanes;
+
+typedef struct sd_ctx sd_ctx;
+
+int sd_default_params(SdParams* p);
+
+/* ProbabilityMapping::ProbabilityMapping(Map*), PM.cc:61: one context per GPU. */
+int sd_create(int device, const SdParams* params /* NULL = defaults */, sd_ctx** out);
+int sd_destroy(sd_ctx* ctx);
+
+/* Key-frame image upload + gradient front end on device: the fields PM.cc reads as kf->im_,
+ * kf->GradImg, kf->GradTheta, kf->I_stddev (PM.cc:186, 201, 214, 457).  K = {fx, fy, cx, cy};
+ * Tcw = 3x4 row-major world-to-camera pose (KeyFrame::GetRotation/GetTranslation, KeyFrame.cc:109-119).
+ * `gray` is a HOST buffer with `stride` bytes per row, borrowed for the duration of the call only when
+ * it is pageable; pinned buffers must stay valid until the next sd_sync. */
+int sd_upload_keyframe(sd_ctx* ctx, int kf_id, const uint8_t* gray, int w, int h, int stride, const float K[4],
+                       const float Tcw[12]);
+/* Same, `gray_dev` already resident in device memory of this context's GPU. */
+int sd_upload_keyframe_device(sd_ctx* ctx, int kf_id, const uint8_t* gray_dev, int w, int h, int stride,
+                              const float K[4], const float Tcw[12]);
+/* KeyFrame::SetPose (KeyFrame.cc:70-84) after BA / loop closing; marks poseChanged (PM.cc:329). */
+int sd_set_pose(sd_ctx* ctx, int kf_id, const float Tcw[12]);
+int sd_release_keyframe(sd_ctx* ctx, int kf_id);
+
+/* SemiDenseLoop per-key-frame half, PM.cc:137-257: ComputeFundamental per neighbour (189-195),
+ * the pixel loop with EpipolarSearch + InverseDepthHypothesisFusion (197-231),
+ * IntraKeyFrameDepthChecking + IntraKeyFrameDepthGrowing (237-238).  The caller supplies what the
+ * reference computes on the host before the loop: the neighbour pick (151-160), the median in-plane
+ * rotation per neighbour in degrees (170-179) and the StereoSearchConstraints interval (184;
+ * NB min_invdepth is the LARGER value, PM.cc:381-382). */
+int sd_semidense(sd_ctx* ctx, int kf_id, const int* nbr_ids, const float* nbr_rot_deg, int n, float min_invdepth,
+                 float max_invdepth);
+
+/* InterKeyFrameDepthChecking, PM.cc:628-799, snapshot semantics (reads the neighbours' maps as
+ * they were after sd_semidense, writes this key frame's `depth_checked`). */
+int sd_interkf_check(sd_ctx* ctx, int kf_id, const int* nbr_ids, int n);
+
+/* UpdateSemiDensePointSet, PM.cc:337-367 (uses depth_checked when present, else depth). */
+int sd_update_pointset(sd_ctx* ctx, int kf_id);
+
+/* Copy results to host buffers (each may be NULL): depth = depth_checked when the inter-KF stage
+ * ran, else the intra-KF map; W*H floats each, points H*3W floats.  Synchronises. */
+int sd_download(sd_ctx* ctx, int kf_id, float* depth, float* sigma, float* points);
+/* Asynchronous variant for pinned host buffers; completes at the next sd_sync. */
+int sd_download_async(sd_ctx* ctx, int kf_id, float* depth, float* sigma, float* points);
+/* Any single plane, for tests: 0 grad, 1 theta, 2 depth (intra), 3 sigma, 4 depth_checked, 5 points. */
+int sd_download_plane(sd_ctx* ctx, int kf_id, int which, float* out);
+int sd_get_istddev(sd_ctx* ctx, int kf_id, float* out);        /* KeyFrame::I_stddev */
+int sd_get_active_count(sd_ctx* ctx, int kf_id, int* out);     /* pixels passing the PM.cc:201 gate */
+int sd_device_ptrs(sd_ctx* ctx, int kf_id, SdDevicePlanes* out);
+/* Replace the (depth, sigma) maps of a key frame from device buffers (tightly packed W*H floats):
+ * how a rank installs a neighbour's maps received over NCCL before sd_interkf_check. */
+int sd_import_maps(sd_ctx* ctx, int kf_id, const float* depth_dev, const float* sigma_dev);
+/* Pack the (depth, sigma) maps of a key frame into device buffers (tightly packed W*H floats). */
+int sd_export_maps(sd_ctx* ctx, int kf_id, float* depth_dev, float* sigma_dev);
+
+int sd_sync(sd_ctx* ctx);
+const char* sd_last_error(sd_ctx* ctx);
+/* cudaStream_t of the compute stream, for callers that order their own device work after it */
+int sd_compute_stream(sd_ctx* ctx, void** stream);
+/* number of kernels this context has launched, and device time of the last timed span */
+int sd_launch_count(sd_ctx* ctx, uint64_t* out);
+/* Per-kernel device timing (CUDA events on the launching stream). enable=1 starts collecting. */
+int sd_timing_enable(sd_ctx* ctx, int enable);
+/* names: "grad", "search", "intra", "grow", "inter", "points"; returns accumulated ms and launches */
+int sd_timing_get(sd_ctx* ctx, const char* name, double* ms, uint64_t* launches);
+int sd_timing_reset(sd_ctx* ctx);
+
+/* ---- host-side helpers that stay on the CPU in the reference too ---- */
+/* StereoSearchConstraints, PM.cc:370-383, on the vector GetAllPointDepths() would return. */
+int sd_stereo_search_constraints(const float* orb_depths, int n, float* min_invdepth, float* max_invdepth);
+/* GetRotInPlane + median, PM.cc:467-484 and 172-177.  Map points by id, id < 0 = none. */
+float sd_rot_in_plane_median(const long long* mp1, const float* ang1, int n1, const long long* mp2,
+                             const float* ang2, int n2);
+/* ComputeFundamental PM.cc:972-987 and the R21/t21 of PM.cc:890-891, OpenCV-exact arithmetic. */
+int sd_pair_geometry(const float K1[4], const float Tcw1[12], const float K2[4], const float Tcw2[12], float F12[9],
+                     float R21[9], float t21[3]);
+
+/* ---- single-pixel probes (run the same device code as the batch kernels; for unit tests) ---- */
+/* EpipolarSearch PM.cc:385-465 for n pixels xy[2*i], xy[2*i+1] of kf1 against kf2.
+ * out[4*i..] = {inverse depth, sigma, best integer uj (or -1), supported} */
+int sd_probe_epipolar(sd_ctx* ctx, int kf1, int kf2, const int* xy, int n, float min_invdepth, float max_invdepth,
+                      float rot_deg, float* out);
+/* InverseDepthHypothesisFusion PM.cc:598-626 on one hypothesis list (n <= SD_MAX_NEIGHBOURS). */
+int sd_probe_fusion(sd_ctx* ctx, const float* depth, const float* sigma, int n, float* out_depth, float* out_sigma,
+                    int* supported);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDPM_H */

@@ -1,0 +1,278 @@
+"""B200-native semi-dense probability mapping (the ProbabilityMapping hot path of
+atlas-jj/ORB-SLAM-free-space-carving).
+
+The product is `lib/libsdpm.so`: hand-written CUDA kernels for sm_100a behind the C ABI declared in
+`include/sdpm.h`; the C++ host mirror of the reference class lives in `host/`.  This Python
+module is only a ctypes binding of that C ABI for the test-suite and bench.py.  There is no CPU
+fallback: importing works anywhere, but `Context()` raises unless the library is built and a
+CUDA device is present.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libsdpm.so")
+INCLUDE_DIR = os.path.join(os.path.dirname(_HERE), "include")
+
+SD_MAX_NEIGHBOURS = 40
+GRAD, THETA, DEPTH, SIGMA, DEPTH_CHECKED, POINTS = range(6)
+
+STATUS = {0: "SD_OK", -1: "SD_ERR_INVALID_ARG", -2: "SD_ERR_UNKNOWN_KEYFRAME", -3: "SD_ERR_NOT_READY",
+          -4: "SD_ERR_CUDA", -5: "SD_ERR_NO_DEVICE", -6: "SD_ERR_SHAPE"}
+
+
+class SdError(RuntimeError):
+    def __init__(self, code, msg=""):
+        super().__init__(f"{STATUS.get(code, code)}: {msg}")
+        self.code = code
+
+
+class SdParams(C.Structure):
+    _fields_ = [("lambdaG", C.c_float), ("lambdaL", C.c_float), ("lambdaTheta", C.c_float), ("lambdaN", C.c_int),
+                ("theta", C.c_double), ("chi2_fuse", C.c_double), ("chi2_inter", C.c_double),
+                ("slope_limit", C.c_float), ("border", C.c_int)]
+
+
+class SdDevicePlanes(C.Structure):
+    _fields_ = [("width", C.c_int), ("height", C.c_int), ("pitch_f32", C.c_int), ("pitch_u8", C.c_int),
+                ("gray", C.c_void_p), ("grad", C.c_void_p), ("theta", C.c_void_p), ("depth", C.c_void_p),
+                ("sigma", C.c_void_p), ("depth_checked", C.c_void_p), ("points", C.c_void_p)]
+
+
+_lib = None
+_fp, _ip, _vp = C.POINTER(C.c_float), C.POINTER(C.c_int), C.c_void_p
+
+# every symbol include/sdpm.h declares: (restype, argtypes)
+SYMBOLS = {
+    "sd_default_params": (C.c_int, [C.POINTER(SdParams)]),
+    "sd_create": (C.c_int, [C.c_int, C.POINTER(SdParams), C.POINTER(_vp)]),
+    "sd_destroy": (C.c_int, [_vp]),
+    "sd_upload_keyframe": (C.c_int, [_vp, C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp]),
+    "sd_upload_keyframe_device": (C.c_int, [_vp, C.c_int, _vp, C.c_int, C.c_int, C.c_int, _fp, _fp]),
+    "sd_set_pose": (C.c_int, [_vp, C.c_int, _fp]),
+    "sd_release_keyframe": (C.c_int, [_vp, C.c_int]),
+    "sd_semidense": (C.c_int, [_vp, C.c_int, _ip, _fp, C.c_int, C.c_float, C.c_float]),
+    "sd_interkf_check": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
+    "sd_update_pointset": (C.c_int, [_vp, C.c_int]),
+    "sd_download": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
+    "sd_download_async": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
+    "sd_download_plane": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "sd_get_istddev": (C.c_int, [_vp, C.c_int, _fp]),
+    "sd_get_active_count": (C.c_int, [_vp, C.c_int, _ip]),
+    "sd_device_ptrs": (C.c_int, [_vp, C.c_int, C.POINTER(SdDevicePlanes)]),
+    "sd_import_maps": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "sd_export_maps": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "sd_sync": (C.c_int, [_vp]),
+    "sd_last_error": (C.c_char_p, [_vp]),
+    "sd_compute_stream": (C.c_int, [_vp, C.POINTER(_vp)]),
+    "sd_launch_count": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "sd_timing_enable": (C.c_int, [_vp, C.c_int]),
+    "sd_timing_get": (C.c_int, [_vp, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
+    "sd_timing_reset": (C.c_int, [_vp]),
+    "sd_stereo_search_constraints": (C.c_int, [_fp, C.c_int, _fp, _fp]),
+    "sd_rot_in_plane_median": (C.c_float, [_vp, _fp, C.c_int, _vp, _fp, C.c_int]),
+    "sd_pair_geometry": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "sd_probe_epipolar": (C.c_int, [_vp, C.c_int, C.c_int, _ip, C.c_int, C.c_float, C.c_float, C.c_float, _fp]),
+    "sd_probe_fusion": (C.c_int, [_vp, _fp, _fp, C.c_int, _fp, _fp, _ip]),
+}
+
+
+def lib():
+    """Load lib/libsdpm.so.  Fails loudly when it has not been built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(f"{LIB_PATH} is missing -- build it with `python __graft_entry__.py build` "
+                               "(there is no CPU fallback for the CUDA path)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)  # AttributeError if the library does not export a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _f(a):
+    a = np.ascontiguousarray(a, dtype=np.float32)
+    return a, a.ctypes.data_as(_fp)
+
+
+def _i(a):
+    a = np.ascontiguousarray(a, dtype=np.int32)
+    return a, a.ctypes.data_as(_ip)
+
+
+def default_params():
+    p = SdParams()
+    lib().sd_default_params(C.byref(p))
+    return p
+
+
+def stereo_search_constraints(depths):
+    """StereoSearchConstraints (PM.cc:370-383): returns (min_depth, max_depth) = inverse-depth interval."""
+    d, dp = _f(depths)
+    mn, mx = C.c_float(), C.c_float()
+    rc = lib().sd_stereo_search_constraints(dp, len(d), C.byref(mn), C.byref(mx))
+    if rc:
+        raise SdError(rc)
+    return mn.value, mx.value
+
+
+def rot_in_plane_median(mp1, ang1, mp2, ang2):
+    m1 = np.ascontiguousarray(mp1, np.int64)
+    m2 = np.ascontiguousarray(mp2, np.int64)
+    a1, a1p = _f(ang1)
+    a2, a2p = _f(ang2)
+    return float(lib().sd_rot_in_plane_median(m1.ctypes.data, a1p, len(m1), m2.ctypes.data, a2p, len(m2)))
+
+
+def pair_geometry(K1, Tcw1, K2, Tcw2):
+    a = [_f(x) for x in (K1, np.asarray(Tcw1).reshape(-1)[:12], K2, np.asarray(Tcw2).reshape(-1)[:12])]
+    F, R, t = (C.c_float * 9)(), (C.c_float * 9)(), (C.c_float * 3)()
+    rc = lib().sd_pair_geometry(a[0][1], a[1][1], a[2][1], a[3][1], F, R, t)
+    if rc:
+        raise SdError(rc)
+    return np.array(F, np.float32).reshape(3, 3), np.array(R, np.float32).reshape(3, 3), np.array(t, np.float32)
+
+
+class Context:
+    """One sd_ctx (one GPU).  Thin wrapper: every method is one C-ABI call."""
+
+    def __init__(self, device=0, params=None):
+        self.L = lib()
+        h = _vp()
+        rc = self.L.sd_create(int(device), C.byref(params) if params is not None else None, C.byref(h))
+        if rc:
+            raise SdError(rc, "sd_create failed (no usable CUDA device?)")
+        self.h = h
+        self.shape = None
+
+    def _ck(self, rc):
+        if rc:
+            raise SdError(rc, (self.L.sd_last_error(self.h) or b"").decode())
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.sd_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def upload_keyframe(self, kf_id, gray, K, Tcw):
+        """gray: HxW uint8 numpy array (or any object with .ctypes / int pointer via upload_keyframe_ptr)."""
+        gray = np.ascontiguousarray(gray, dtype=np.uint8)
+        h, w = gray.shape
+        self.upload_keyframe_ptr(kf_id, gray.ctypes.data, w, h, w, K, Tcw)
+
+    def upload_keyframe_ptr(self, kf_id, ptr, w, h, stride, K, Tcw, device=False):
+        _, kp = _f(K)
+        _, tp = _f(np.asarray(Tcw).reshape(-1)[:12])
+        fn = self.L.sd_upload_keyframe_device if device else self.L.sd_upload_keyframe
+        self._ck(fn(self.h, int(kf_id), ptr, w, h, stride, kp, tp))
+        self.shape = (h, w)
+
+    def set_pose(self, kf_id, Tcw):
+        _, tp = _f(np.asarray(Tcw).reshape(-1)[:12])
+        self._ck(self.L.sd_set_pose(self.h, int(kf_id), tp))
+
+    def release_keyframe(self, kf_id):
+        self._ck(self.L.sd_release_keyframe(self.h, int(kf_id)))
+
+    def semidense(self, kf_id, nbr_ids, nbr_rot, min_depth, max_depth):
+        ids, ip = _i(nbr_ids)
+        rot, rp = _f(nbr_rot)
+        self._ck(self.L.sd_semidense(self.h, int(kf_id), ip, rp, len(ids), float(min_depth), float(max_depth)))
+
+    def interkf_check(self, kf_id, nbr_ids):
+        ids, ip = _i(nbr_ids)
+        self._ck(self.L.sd_interkf_check(self.h, int(kf_id), ip, len(ids)))
+
+    def update_pointset(self, kf_id):
+        self._ck(self.L.sd_update_pointset(self.h, int(kf_id)))
+
+    def download(self, kf_id, points=False):
+        h, w = self.shape
+        d = np.empty((h, w), np.float32)
+        s = np.empty((h, w), np.float32)
+        p = np.empty((h, 3 * w), np.float32) if points else None
+        self._ck(self.L.sd_download(self.h, int(kf_id), d.ctypes.data, s.ctypes.data, p.ctypes.data if points else None))
+        return (d, s, p) if points else (d, s)
+
+    def download_async_ptr(self, kf_id, depth_ptr, sigma_ptr, points_ptr=None):
+        self._ck(self.L.sd_download_async(self.h, int(kf_id), depth_ptr, sigma_ptr, points_ptr))
+
+    def plane(self, kf_id, which):
+        h, w = self.shape
+        out = np.empty((h, 3 * w if which == POINTS else w), np.float32)
+        self._ck(self.L.sd_download_plane(self.h, int(kf_id), which, out.ctypes.data))
+        return out
+
+    def istddev(self, kf_id):
+        v = C.c_float()
+        self._ck(self.L.sd_get_istddev(self.h, int(kf_id), C.byref(v)))
+        return v.value
+
+    def active_count(self, kf_id):
+        v = C.c_int()
+        self._ck(self.L.sd_get_active_count(self.h, int(kf_id), C.byref(v)))
+        return v.value
+
+    def device_ptrs(self, kf_id):
+        p = SdDevicePlanes()
+        self._ck(self.L.sd_device_ptrs(self.h, int(kf_id), C.byref(p)))
+        return p
+
+    def import_maps(self, kf_id, depth_dev_ptr, sigma_dev_ptr):
+        self._ck(self.L.sd_import_maps(self.h, int(kf_id), depth_dev_ptr, sigma_dev_ptr))
+
+    def export_maps(self, kf_id, depth_dev_ptr, sigma_dev_ptr):
+        self._ck(self.L.sd_export_maps(self.h, int(kf_id), depth_dev_ptr, sigma_dev_ptr))
+
+    def sync(self):
+        self._ck(self.L.sd_sync(self.h))
+
+    def compute_stream(self):
+        s = _vp()
+        self._ck(self.L.sd_compute_stream(self.h, C.byref(s)))
+        return s.value
+
+    def launch_count(self):
+        v = C.c_uint64()
+        self._ck(self.L.sd_launch_count(self.h, C.byref(v)))
+        return v.value
+
+    def timing_enable(self, on=True):
+        self._ck(self.L.sd_timing_enable(self.h, 1 if on else 0))
+
+    def timing_reset(self):
+        self._ck(self.L.sd_timing_reset(self.h))
+
+    def timing(self):
+        out = {}
+        for name in ("grad", "search", "intra", "grow", "inter", "points"):
+            ms, n = C.c_double(), C.c_uint64()
+            self._ck(self.L.sd_timing_get(self.h, name.encode(), C.byref(ms), C.byref(n)))
+            out[name] = (ms.value, n.value)
+        return out
+
+    def probe_epipolar(self, kf1, kf2, xy, min_depth, max_depth, rot):
+        xy, xp = _i(np.asarray(xy).reshape(-1))
+        n = len(xy) // 2
+        out = np.empty((n, 4), np.float32)
+        self._ck(self.L.sd_probe_epipolar(self.h, int(kf1), int(kf2), xp, n, float(min_depth), float(max_depth), float(rot),
+                                          out.ctypes.data_as(_fp)))
+        return out
+
+    def probe_fusion(self, depth, sigma):
+        d, dp = _f(depth)
+        s, sp = _f(sigma)
+        od, os_, sup = C.c_float(), C.c_float(), C.c_int()
+        self._ck(self.L.sd_probe_fusion(self.h, dp, sp, len(d), C.byref(od), C.byref(os_), C.byref(sup)))
+        return od.value, os_.value, bool(sup.value)

@@ -1,0 +1,751 @@
+// C ABI (include/sdpm.h) over the CUDA kernels in sdpm_kernels.cuh: the context that owns the
+// device-resident key-frame planes, the three streams (upload+K0 / K1..K5 / download) and the
+// per-pair host math.  No CPU fallback exists: every stage is a kernel launch.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "../../include/sdpm.h"
+#include "pair_geometry.h"
+#include "sdpm_kernels.cuh"
+
+using namespace sdpm;
+
+namespace {
+
+enum { T_GRAD = 0, T_SEARCH, T_INTRA, T_GROW, T_INTER, T_POINTS, T_COUNT };
+const char* kTimerNames[T_COUNT] = {"grad", "search", "intra", "grow", "inter", "points"};
+
+struct Slot {
+    int id = -1;
+    float K[4] = {0, 0, 0, 0};
+    float Rcw[9], tcw[3], Twc[16];
+    uint8_t* slab = nullptr;  // one allocation for everything below except points
+    uint8_t* gray = nullptr;
+    float *grad = nullptr, *theta = nullptr, *gate = nullptr, *depth = nullptr, *sigma = nullptr, *depth_chk = nullptr;
+    float* points = nullptr;
+    uint32_t* list = nullptr;
+    KfMeta* meta = nullptr;
+    bool has_semidense = false, has_checked = false, has_points = false, pose_changed = false;
+    cudaEvent_t ev_up = nullptr;  // upload + K0 done (s_up)
+    cudaEvent_t ev_dn = nullptr;  // last download issued (s_dn)
+    bool dn_pending = false;
+};
+
+struct TimedSpan {
+    int which;
+    cudaEvent_t a, b;
+};
+
+}  // namespace
+
+struct sd_ctx {
+    int device = 0;
+    SdParams P;
+    int W = 0, H = 0, pitch_f = 0, pitch_u8 = 0;
+    cudaStream_t s_up = nullptr, s_main = nullptr, s_dn = nullptr;
+    cudaEvent_t ev_tmp = nullptr;
+    std::unordered_map<int, Slot*> kfs;
+    std::vector<Slot*> free_slots;
+    float *tmp_depth = nullptr, *tmp_sigma = nullptr;
+    std::string err;
+    uint64_t launches = 0;
+    bool timing = false;
+    std::vector<TimedSpan> spans;
+    std::vector<cudaEvent_t> ev_pool;
+    double t_ms[T_COUNT] = {0};
+    uint64_t t_n[T_COUNT] = {0};
+    float chi_fuse_f = 0, chi_inter_f = 0;
+};
+
+namespace {
+
+int fail(sd_ctx* c, int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    if (c) c->err = buf;
+    return code;
+}
+
+#define CU(c, call)                                                                                      \
+    do {                                                                                                 \
+        cudaError_t e__ = (call);                                                                        \
+        if (e__ != cudaSuccess) return fail(c, SD_ERR_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e__), __FILE__, __LINE__); \
+    } while (0)
+
+Slot* find(sd_ctx* c, int id) {
+    auto it = c->kfs.find(id);
+    return it == c->kfs.end() ? nullptr : it->second;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+int alloc_slot(sd_ctx* c, Slot** out) {
+    if (!c->free_slots.empty()) {
+        *out = c->free_slots.back();
+        c->free_slots.pop_back();
+        return SD_OK;
+    }
+    Slot* s = new Slot();
+    const size_t fplane = align_up((size_t)c->pitch_f * c->H * sizeof(float), 256);
+    const size_t uplane = align_up((size_t)c->pitch_u8 * c->H, 256);
+    const size_t lplane = align_up((size_t)c->W * c->H * sizeof(uint32_t), 256);
+    const size_t total = uplane + 6 * fplane + lplane + 256;
+    cudaError_t e = cudaMalloc(&s->slab, total);
+    if (e != cudaSuccess) {
+        delete s;
+        return fail(c, SD_ERR_CUDA, "cudaMalloc(%zu): %s", total, cudaGetErrorString(e));
+    }
+    uint8_t* p = s->slab;
+    s->gray = p; p += uplane;
+    s->grad = (float*)p; p += fplane;
+    s->theta = (float*)p; p += fplane;
+    s->gate = (float*)p; p += fplane;
+    s->depth = (float*)p; p += fplane;
+    s->sigma = (float*)p; p += fplane;
+    s->depth_chk = (float*)p; p += fplane;
+    s->list = (uint32_t*)p; p += lplane;
+    s->meta = (KfMeta*)p;
+    cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&s->ev_dn, cudaEventDisableTiming);
+    *out = s;
+    return SD_OK;
+}
+
+void free_slot(Slot* s) {
+    if (!s) return;
+    cudaFree(s->slab);
+    cudaFree(s->points);
+    if (s->ev_up) cudaEventDestroy(s->ev_up);
+    if (s->ev_dn) cudaEventDestroy(s->ev_dn);
+    delete s;
+}
+
+cudaEvent_t pool_event(sd_ctx* c) {
+    if (!c->ev_pool.empty()) {
+        cudaEvent_t e = c->ev_pool.back();
+        c->ev_pool.pop_back();
+        return e;
+    }
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    return e;
+}
+
+struct ScopedTimer {  // CUDA events on the launching stream around one kernel
+    sd_ctx* c;
+    cudaStream_t s;
+    int which;
+    cudaEvent_t a = nullptr, b = nullptr;
+    ScopedTimer(sd_ctx* c_, cudaStream_t s_, int w) : c(c_), s(s_), which(w) {
+        if (c->timing) {
+            a = pool_event(c);
+            b = pool_event(c);
+            cudaEventRecord(a, s);
+        }
+    }
+    ~ScopedTimer() {
+        c->launches++;
+        if (a) {
+            cudaEventRecord(b, s);
+            c->spans.push_back({which, a, b});
+        }
+    }
+};
+
+void collect_spans(sd_ctx* c) {
+    for (auto& sp : c->spans) {
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) {
+            c->t_ms[sp.which] += ms;
+            c->t_n[sp.which]++;
+        }
+        c->ev_pool.push_back(sp.a);
+        c->ev_pool.push_back(sp.b);
+    }
+    c->spans.clear();
+}
+
+void set_pose_fields(Slot* s, const float Tcw[12]) {
+    for (int r = 0; r < 3; ++r) {
+        for (int col = 0; col < 3; ++col) s->Rcw[r * 3 + col] = Tcw[r * 4 + col];
+        s->tcw[r] = Tcw[r * 4 + 3];
+    }
+    geom::pose_inverse(s->Rcw, s->tcw, s->Twc);
+}
+
+int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int w, int h, int stride, const float K[4],
+                  const float Tcw[12]) {
+    if (!c || !gray || !K || !Tcw || w < 8 || h < 8 || stride < w || w > 65535 || h > 65535)
+        return fail(c, SD_ERR_INVALID_ARG, "sd_upload_keyframe: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    if (c->W == 0) {
+        c->W = w;
+        c->H = h;
+        c->pitch_f = (int)align_up(w, 32);
+        c->pitch_u8 = (int)align_up(w, 128);
+        const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
+        CU(c, cudaMalloc(&c->tmp_depth, fplane));
+        CU(c, cudaMalloc(&c->tmp_sigma, fplane));
+    } else if (c->W != w || c->H != h) {
+        return fail(c, SD_ERR_SHAPE, "key frame %d is %dx%d, context is %dx%d", kf_id, w, h, c->W, c->H);
+    }
+    Slot* s = find(c, kf_id);
+    if (s) {
+        // planes are being replaced: wait for everything already queued that may still read them
+        CU(c, cudaEventRecord(c->ev_tmp, c->s_main));
+        CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
+        CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
+        CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
+    } else {
+        int rc = alloc_slot(c, &s);
+        if (rc != SD_OK) return rc;
+        s->id = kf_id;
+        c->kfs[kf_id] = s;
+    }
+    s->has_semidense = s->has_checked = s->has_points = s->pose_changed = false;
+    s->dn_pending = false;
+    std::memcpy(s->K, K, sizeof(s->K));
+    set_pose_fields(s, Tcw);
+
+    CU(c, cudaMemcpy2DAsync(s->gray, c->pitch_u8, gray, stride, w, h, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->s_up));
+    CU(c, cudaMemsetAsync(s->meta, 0, sizeof(KfMeta), c->s_up));
+    {
+        ScopedTimer t(c, c->s_up, T_GRAD);
+        dim3 blk(K0_TX, K0_TY), grd((w + K0_TW - 1) / K0_TW, (h + K0_TY - 1) / K0_TY);
+        k0_gradient<<<grd, blk, 0, c->s_up>>>(s->gray, c->pitch_u8, w, h, s->grad, s->theta, s->gate, c->pitch_f, s->list, s->meta,
+                                              c->P.lambdaG, c->P.border);
+    }
+    k0_finalize<<<1, 1, 0, c->s_up>>>(s->meta, w, h);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(s->ev_up, c->s_up));
+    return SD_OK;
+}
+
+void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
+    A.W = c->W; A.H = c->H; A.pitch_f = c->pitch_f; A.pitch_u8 = c->pitch_u8;
+    A.border = c->P.border; A.lambdaN = c->P.lambdaN;
+    A.fx = s->K[0]; A.fy = s->K[1]; A.cx = s->K[2]; A.cy = s->K[3];
+    A.lambdaL = c->P.lambdaL; A.lambdaTheta = c->P.lambdaTheta; A.slope = c->P.slope_limit;
+    A.chi_fuse = c->chi_fuse_f;
+    A.THETA = c->P.theta;
+    A.inv_THETA = 1 / c->P.theta;
+    A.img = s->gray; A.grad = s->grad; A.gate = s->gate; A.theta = s->theta;
+    A.list = s->list; A.meta = s->meta;
+    A.count_override = -1;
+    A.depth = s->depth; A.sigma = s->sigma;
+    A.probe_out = nullptr;
+}
+
+void fill_nbr(Slot* s, Slot* nb, float rot, NbrConst& N) {
+    geom::fundamental(s->K, s->Rcw, s->tcw, nb->K, nb->Rcw, nb->tcw, N.F);
+    geom::relative_pose(s->Rcw, s->tcw, nb->Rcw, nb->tcw, N.R, N.t);
+    N.rot = rot;
+    N.img = nb->gray; N.grad = nb->grad; N.gate = nb->gate; N.meta = nb->meta;
+}
+
+}  // namespace
+
+extern "C" {
+
+int sd_default_params(SdParams* p) {
+    if (!p) return SD_ERR_INVALID_ARG;
+    p->lambdaG = 8;
+    p->lambdaL = 80;
+    p->lambdaTheta = 45;
+    p->lambdaN = 3;
+    p->theta = 0.23;
+    p->chi2_fuse = 5.99;
+    p->chi2_inter = 3.84;
+    p->slope_limit = 4;
+    p->border = 2;
+    return SD_OK;
+}
+
+int sd_create(int device, const SdParams* params, sd_ctx** out) {
+    if (!out) return SD_ERR_INVALID_ARG;
+    *out = nullptr;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0 || device < 0 || device >= ndev) return SD_ERR_NO_DEVICE;
+    if (cudaSetDevice(device) != cudaSuccess) return SD_ERR_NO_DEVICE;
+    sd_ctx* c = new sd_ctx();
+    c->device = device;
+    if (params) c->P = *params; else sd_default_params(&c->P);
+    if (c->P.border < 1 || c->P.lambdaN < 1 || !(c->P.theta > 0)) {
+        delete c;
+        return SD_ERR_INVALID_ARG;
+    }
+    c->chi_fuse_f = geom::round_up_to_float(c->P.chi2_fuse);
+    c->chi_inter_f = geom::round_up_to_float(c->P.chi2_inter);
+    if (cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->s_dn, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_tmp, cudaEventDisableTiming) != cudaSuccess) {
+        delete c;
+        return SD_ERR_CUDA;
+    }
+    *out = c;
+    return SD_OK;
+}
+
+int sd_destroy(sd_ctx* c) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (auto& kv : c->kfs) free_slot(kv.second);
+    for (auto* s : c->free_slots) free_slot(s);
+    for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
+    for (auto e : c->ev_pool) cudaEventDestroy(e);
+    cudaFree(c->tmp_depth);
+    cudaFree(c->tmp_sigma);
+    if (c->ev_tmp) cudaEventDestroy(c->ev_tmp);
+    cudaStreamDestroy(c->s_up);
+    cudaStreamDestroy(c->s_main);
+    cudaStreamDestroy(c->s_dn);
+    delete c;
+    return SD_OK;
+}
+
+int sd_upload_keyframe(sd_ctx* c, int kf_id, const uint8_t* gray, int w, int h, int stride, const float K[4], const float Tcw[12]) {
+    return upload_common(c, kf_id, gray, false, w, h, stride, K, Tcw);
+}
+
+int sd_upload_keyframe_device(sd_ctx* c, int kf_id, const uint8_t* gray_dev, int w, int h, int stride, const float K[4],
+                              const float Tcw[12]) {
+    return upload_common(c, kf_id, gray_dev, true, w, h, stride, K, Tcw);
+}
+
+int sd_set_pose(sd_ctx* c, int kf_id, const float Tcw[12]) {
+    if (!c || !Tcw) return fail(c, SD_ERR_INVALID_ARG, "sd_set_pose: bad argument");
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    set_pose_fields(s, Tcw);
+    s->pose_changed = true;
+    return SD_OK;
+}
+
+int sd_release_keyframe(sd_ctx* c, int kf_id) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    auto it = c->kfs.find(kf_id);
+    if (it == c->kfs.end()) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaDeviceSynchronize());  // nothing queued may still reference the planes
+    c->free_slots.push_back(it->second);
+    c->kfs.erase(it);
+    return SD_OK;
+}
+
+int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_deg, int n, float min_invdepth, float max_invdepth) {
+    if (!c || !nbr_ids || n < 1 || n > SD_MAX_NEIGHBOURS) return fail(c, SD_ERR_INVALID_ARG, "sd_semidense: bad argument (n=%d)", n);
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    static thread_local SearchArgs A;
+    fill_search_common(c, s, A);
+    A.n = n;
+    A.mind = min_invdepth;
+    A.maxd = max_invdepth;
+    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
+    for (int j = 0; j < n; ++j) {
+        Slot* nb = find(c, nbr_ids[j]);
+        if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
+        fill_nbr(s, nb, nbr_rot_deg ? nbr_rot_deg[j] : 0.f, A.nb[j]);
+        CU(c, cudaStreamWaitEvent(c->s_main, nb->ev_up, 0));
+    }
+    if (s->dn_pending) {  // a download of the old maps may still be in flight
+        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        s->dn_pending = false;
+    }
+    const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
+    CU(c, cudaMemsetAsync(s->depth, 0, fplane, c->s_main));
+    CU(c, cudaMemsetAsync(s->sigma, 0, fplane, c->s_main));
+    {
+        ScopedTimer t(c, c->s_main, T_SEARCH);
+        const int max_entries = c->W * c->H;
+        const int blocks = (max_entries + K1_WARPS * 32 - 1) / (K1_WARPS * 32);
+        k1_search<<<blocks, K1_WARPS * 32, 0, c->s_main>>>(A);
+    }
+    StencilArgs S;
+    S.W = c->W; S.H = c->H; S.pitch_f = c->pitch_f; S.border = c->P.border;
+    S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f; S.grad = s->grad;
+    dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
+    {
+        ScopedTimer t(c, c->s_main, T_INTRA);
+        S.depth_in = s->depth; S.sigma_in = s->sigma; S.depth_out = c->tmp_depth; S.sigma_out = c->tmp_sigma;
+        k2_intra_check<<<grd, blk, 0, c->s_main>>>(S);
+    }
+    {
+        ScopedTimer t(c, c->s_main, T_GROW);
+        S.depth_in = c->tmp_depth; S.sigma_in = c->tmp_sigma; S.depth_out = s->depth; S.sigma_out = s->sigma;
+        k3_intra_grow<<<grd, blk, 0, c->s_main>>>(S);
+    }
+    CU(c, cudaGetLastError());
+    s->has_semidense = true;
+    s->has_checked = false;
+    s->has_points = false;
+    return SD_OK;
+}
+
+int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
+    if (!c || !nbr_ids || n < 1 || n > SD_MAX_NEIGHBOURS) return fail(c, SD_ERR_INVALID_ARG, "sd_interkf_check: bad argument (n=%d)", n);
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    static thread_local InterArgs A;
+    A.W = c->W; A.H = c->H; A.pitch_f = c->pitch_f; A.n = n; A.lambdaN = c->P.lambdaN;
+    A.fx = s->K[0]; A.fy = s->K[1]; A.cx = s->K[2]; A.cy = s->K[3];
+    A.chi_inter = c->chi_inter_f;
+    A.depth_in = s->depth;
+    A.depth_out = s->depth_chk;
+    for (int j = 0; j < n; ++j) {
+        Slot* nb = find(c, nbr_ids[j]);
+        if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
+        if (!nb->has_semidense) return fail(c, SD_ERR_NOT_READY, "neighbour key frame %d has no semi-dense maps", nbr_ids[j]);
+        InterNbr& N = A.nb[j];
+        geom::relative_pose(s->Rcw, s->tcw, nb->Rcw, nb->tcw, N.R, N.t);
+        N.fx = nb->K[0]; N.fy = nb->K[1]; N.cx = nb->K[2]; N.cy = nb->K[3];
+        N.depth = nb->depth;
+        N.sigma = nb->sigma;
+    }
+    if (s->dn_pending) {
+        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        s->dn_pending = false;
+    }
+    {
+        ScopedTimer t(c, c->s_main, T_INTER);
+        dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
+        k4_inter_check<<<grd, blk, 0, c->s_main>>>(A);
+    }
+    CU(c, cudaGetLastError());
+    s->has_checked = true;
+    s->has_points = false;
+    return SD_OK;
+}
+
+int sd_update_pointset(sd_ctx* c, int kf_id) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    if (!s->points) CU(c, cudaMalloc(&s->points, (size_t)c->W * c->H * 3 * sizeof(float)));
+    if (s->dn_pending) {
+        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        s->dn_pending = false;
+    }
+    PointArgs A;
+    A.W = c->W; A.H = c->H; A.pitch_f = c->pitch_f;
+    A.fx = s->K[0]; A.fy = s->K[1]; A.cx = s->K[2]; A.cy = s->K[3];
+    std::memcpy(A.Twc, s->Twc, sizeof(A.Twc));
+    A.depth = s->has_checked ? s->depth_chk : s->depth;
+    A.points = s->points;
+    {
+        ScopedTimer t(c, c->s_main, T_POINTS);
+        dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
+        k5_pointset<<<grd, blk, 0, c->s_main>>>(A);
+    }
+    CU(c, cudaGetLastError());
+    s->has_points = true;
+    s->pose_changed = false;
+    return SD_OK;
+}
+
+int sd_download_async(sd_ctx* c, int kf_id, float* depth, float* sigma, float* points) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
+    if (points && !s->has_points) return fail(c, SD_ERR_NOT_READY, "key frame %d has no point set", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaEventRecord(c->ev_tmp, c->s_main));
+    CU(c, cudaStreamWaitEvent(c->s_dn, c->ev_tmp, 0));
+    const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    if (depth) CU(c, cudaMemcpy2DAsync(depth, wb, s->has_checked ? s->depth_chk : s->depth, pb, wb, c->H, cudaMemcpyDeviceToHost, c->s_dn));
+    if (sigma) CU(c, cudaMemcpy2DAsync(sigma, wb, s->sigma, pb, wb, c->H, cudaMemcpyDeviceToHost, c->s_dn));
+    if (points) CU(c, cudaMemcpyAsync(points, s->points, (size_t)c->W * c->H * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->s_dn));
+    CU(c, cudaEventRecord(s->ev_dn, c->s_dn));
+    s->dn_pending = true;
+    return SD_OK;
+}
+
+int sd_download(sd_ctx* c, int kf_id, float* depth, float* sigma, float* points) {
+    int rc = sd_download_async(c, kf_id, depth, sigma, points);
+    if (rc != SD_OK) return rc;
+    CU(c, cudaStreamSynchronize(c->s_dn));
+    return SD_OK;
+}
+
+int sd_download_plane(sd_ctx* c, int kf_id, int which, float* out) {
+    if (!c || !out) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    const float* src = nullptr;
+    switch (which) {
+        case 0: src = s->grad; break;
+        case 1: src = s->theta; break;
+        case 2: src = s->has_semidense ? s->depth : nullptr; break;
+        case 3: src = s->has_semidense ? s->sigma : nullptr; break;
+        case 4: src = s->has_checked ? s->depth_chk : nullptr; break;
+        case 5: src = s->has_points ? s->points : nullptr; break;
+        default: return fail(c, SD_ERR_INVALID_ARG, "sd_download_plane: which=%d", which);
+    }
+    if (!src) return fail(c, SD_ERR_NOT_READY, "plane %d of key frame %d not computed", which, kf_id);
+    CU(c, cudaStreamSynchronize(c->s_up));
+    CU(c, cudaStreamSynchronize(c->s_main));
+    const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    if (which == 5) CU(c, cudaMemcpy(out, src, (size_t)c->W * c->H * 3 * sizeof(float), cudaMemcpyDeviceToHost));
+    else CU(c, cudaMemcpy2D(out, wb, src, pb, wb, c->H, cudaMemcpyDeviceToHost));
+    return SD_OK;
+}
+
+int sd_get_istddev(sd_ctx* c, int kf_id, float* out) {
+    if (!c || !out) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->s_up));
+    KfMeta m;
+    CU(c, cudaMemcpy(&m, s->meta, sizeof(m), cudaMemcpyDeviceToHost));
+    *out = m.istddev;
+    return SD_OK;
+}
+
+int sd_get_active_count(sd_ctx* c, int kf_id, int* out) {
+    if (!c || !out) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->s_up));
+    KfMeta m;
+    CU(c, cudaMemcpy(&m, s->meta, sizeof(m), cudaMemcpyDeviceToHost));
+    *out = m.active_count;
+    return SD_OK;
+}
+
+int sd_device_ptrs(sd_ctx* c, int kf_id, SdDevicePlanes* out) {
+    if (!c || !out) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    out->width = c->W; out->height = c->H; out->pitch_f32 = c->pitch_f; out->pitch_u8 = c->pitch_u8;
+    out->gray = s->gray; out->grad = s->grad; out->theta = s->theta;
+    out->depth = s->has_semidense ? s->depth : nullptr;
+    out->sigma = s->has_semidense ? s->sigma : nullptr;
+    out->depth_checked = s->has_checked ? s->depth_chk : nullptr;
+    out->points = s->has_points ? s->points : nullptr;
+    return SD_OK;
+}
+
+int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* sigma_dev) {
+    if (!c || !depth_dev || !sigma_dev) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    CU(c, cudaMemcpy2DAsync(s->depth, pb, depth_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
+    CU(c, cudaMemcpy2DAsync(s->sigma, pb, sigma_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
+    s->has_semidense = true;
+    s->has_checked = false;
+    return SD_OK;
+}
+
+int sd_export_maps(sd_ctx* c, int kf_id, float* depth_dev, float* sigma_dev) {
+    if (!c || !depth_dev || !sigma_dev) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    CU(c, cudaMemcpy2DAsync(depth_dev, wb, s->depth, pb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
+    CU(c, cudaMemcpy2DAsync(sigma_dev, wb, s->sigma, pb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
+    return SD_OK;
+}
+
+int sd_sync(sd_ctx* c) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaStreamSynchronize(c->s_up));
+    CU(c, cudaStreamSynchronize(c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_dn));
+    for (auto& kv : c->kfs) kv.second->dn_pending = false;
+    if (c->timing) collect_spans(c);
+    return SD_OK;
+}
+
+const char* sd_last_error(sd_ctx* c) { return c ? c->err.c_str() : "null context"; }
+
+int sd_compute_stream(sd_ctx* c, void** stream) {
+    if (!c || !stream) return SD_ERR_INVALID_ARG;
+    *stream = (void*)c->s_main;
+    return SD_OK;
+}
+
+int sd_launch_count(sd_ctx* c, uint64_t* out) {
+    if (!c || !out) return SD_ERR_INVALID_ARG;
+    *out = c->launches;
+    return SD_OK;
+}
+
+int sd_timing_enable(sd_ctx* c, int enable) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    c->timing = enable != 0;
+    return SD_OK;
+}
+
+int sd_timing_get(sd_ctx* c, const char* name, double* ms, uint64_t* launches) {
+    if (!c || !name) return SD_ERR_INVALID_ARG;
+    int rc = sd_sync(c);
+    if (rc != SD_OK) return rc;
+    collect_spans(c);
+    for (int i = 0; i < T_COUNT; ++i)
+        if (!std::strcmp(name, kTimerNames[i])) {
+            if (ms) *ms = c->t_ms[i];
+            if (launches) *launches = c->t_n[i];
+            return SD_OK;
+        }
+    return fail(c, SD_ERR_INVALID_ARG, "unknown timer %s", name);
+}
+
+int sd_timing_reset(sd_ctx* c) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    int rc = sd_sync(c);
+    if (rc != SD_OK) return rc;
+    collect_spans(c);
+    for (int i = 0; i < T_COUNT; ++i) { c->t_ms[i] = 0; c->t_n[i] = 0; }
+    return SD_OK;
+}
+
+// ---- host-side helpers ----
+
+int sd_stereo_search_constraints(const float* d, int n, float* min_invdepth, float* max_invdepth) {
+    if (!d || n < 1 || !min_invdepth || !max_invdepth) return SD_ERR_INVALID_ARG;
+    // PM.cc:373-382.  std::accumulate / std::inner_product are seeded with 0.0: double accumulators.
+    double acc = 0.0;
+    for (int i = 0; i < n; ++i) acc = acc + d[i];
+    const float sum = (float)acc;
+    const float mean = sum / (float)(size_t)n;
+    double vacc = 0.0;
+    for (int i = 0; i < n; ++i) {
+        const float df = d[i] - mean;
+        vacc = vacc + (df * df);
+    }
+    const float variance = (float)(vacc / (double)(size_t)n);
+    const float stdev = std::sqrt(variance);
+    *max_invdepth = 1 / (mean + 2 * stdev);
+    *min_invdepth = 1 / (mean - 2 * stdev);
+    return SD_OK;
+}
+
+float sd_rot_in_plane_median(const long long* mp1, const float* ang1, int n1, const long long* mp2, const float* ang2, int n2) {
+    // PM.cc:467-484: every (idx1, idx2) pair observing the same map point contributes angle2-angle1
+    // unless either angle is negative; then the lower median, PM.cc:172-177.  The pair set is the
+    // same as the reference's O(n1*n2) pointer scan; it is built through a hash of kf2's points.
+    std::unordered_multimap<long long, int> by_point;
+    by_point.reserve((size_t)n2 * 2);
+    for (int i = 0; i < n2; ++i)
+        if (mp2[i] >= 0) by_point.emplace(mp2[i], i);
+    std::vector<float> rot;
+    for (int i = 0; i < n1; ++i) {
+        if (mp1[i] < 0) continue;
+        auto range = by_point.equal_range(mp1[i]);
+        for (auto it = range.first; it != range.second; ++it) {
+            const float a1 = ang1[i], a2 = ang2[it->second];
+            if (a1 < 0 || a2 < 0) continue;
+            rot.push_back(a2 - a1);
+        }
+    }
+    if (rot.empty()) return 0.f;
+    std::sort(rot.begin(), rot.end());
+    return rot[(rot.size() - 1) / 2];
+}
+
+int sd_pair_geometry(const float K1[4], const float Tcw1[12], const float K2[4], const float Tcw2[12], float F12[9], float R21[9],
+                     float t21[3]) {
+    if (!K1 || !Tcw1 || !K2 || !Tcw2 || !F12 || !R21 || !t21) return SD_ERR_INVALID_ARG;
+    float R1[9], t1[3], R2[9], t2[3];
+    for (int r = 0; r < 3; ++r) {
+        for (int col = 0; col < 3; ++col) { R1[r * 3 + col] = Tcw1[r * 4 + col]; R2[r * 3 + col] = Tcw2[r * 4 + col]; }
+        t1[r] = Tcw1[r * 4 + 3];
+        t2[r] = Tcw2[r * 4 + 3];
+    }
+    geom::fundamental(K1, R1, t1, K2, R2, t2, F12);
+    geom::relative_pose(R1, t1, R2, t2, R21, t21);
+    return SD_OK;
+}
+
+// ---- probes ----
+
+int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float min_invdepth, float max_invdepth, float rot_deg, float* out) {
+    if (!c || !xy || !out || n < 1) return fail(c, SD_ERR_INVALID_ARG, "sd_probe_epipolar: bad argument");
+    Slot* s = find(c, kf1);
+    Slot* nb = find(c, kf2);
+    if (!s || !nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d or %d", kf1, kf2);
+    CU(c, cudaSetDevice(c->device));
+    std::vector<uint32_t> entries(n);
+    for (int i = 0; i < n; ++i) {
+        const int x = xy[2 * i], y = xy[2 * i + 1];
+        if (x < 0 || x >= c->W || y < 0 || y >= c->H) return fail(c, SD_ERR_INVALID_ARG, "probe pixel (%d,%d) outside image", x, y);
+        entries[i] = ((uint32_t)y << 16) | (uint32_t)x;
+    }
+    uint32_t* d_list = nullptr;
+    float* d_out = nullptr;
+    CU(c, cudaMalloc(&d_list, n * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&d_out, (size_t)n * 4 * sizeof(float)));
+    CU(c, cudaStreamSynchronize(c->s_up));
+    CU(c, cudaMemcpyAsync(d_list, entries.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, c->s_main));
+    static thread_local SearchArgs A;
+    fill_search_common(c, s, A);
+    A.n = 1;
+    A.mind = min_invdepth;
+    A.maxd = max_invdepth;
+    A.list = d_list;
+    A.count_override = n;
+    A.probe_out = d_out;
+    fill_nbr(s, nb, rot_deg, A.nb[0]);
+    const int blocks = (n + K1_WARPS * 32 - 1) / (K1_WARPS * 32);
+    k1_search<<<blocks, K1_WARPS * 32, 0, c->s_main>>>(A);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(out, d_out, (size_t)n * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_main));
+    cudaFree(d_list);
+    cudaFree(d_out);
+    return SD_OK;
+}
+
+int sd_probe_fusion(sd_ctx* c, const float* depth, const float* sigma, int n, float* out_depth, float* out_sigma, int* supported) {
+    if (!c || !depth || !sigma || n < 0 || n > SD_MAX_NEIGHBOURS || !out_depth || !out_sigma || !supported)
+        return fail(c, SD_ERR_INVALID_ARG, "sd_probe_fusion: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    float* d = nullptr;
+    CU(c, cudaMalloc(&d, (2 * SD_MAX_NEIGHBOURS + 4) * sizeof(float)));
+    if (n) {
+        CU(c, cudaMemcpyAsync(d, depth, n * sizeof(float), cudaMemcpyHostToDevice, c->s_main));
+        CU(c, cudaMemcpyAsync(d + SD_MAX_NEIGHBOURS, sigma, n * sizeof(float), cudaMemcpyHostToDevice, c->s_main));
+    }
+    k1_fusion_probe<<<1, 1, 0, c->s_main>>>(d, d + SD_MAX_NEIGHBOURS, n, c->P.lambdaN, c->chi_fuse_f, d + 2 * SD_MAX_NEIGHBOURS);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    float r[3];
+    CU(c, cudaMemcpyAsync(r, d + 2 * SD_MAX_NEIGHBOURS, sizeof(r), cudaMemcpyDeviceToHost, c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_main));
+    cudaFree(d);
+    *out_depth = r[0];
+    *out_sigma = r[1];
+    *supported = r[2] != 0.f;
+    return SD_OK;
+}
+
+}  // extern "C"
