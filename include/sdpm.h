@@ -122,6 +122,10 @@ const char* sd_last_error(sd_ctx* ctx);
 int sd_compute_stream(sd_ctx* ctx, void** stream);
 /* number of kernels this context has launched, and device time of the last timed span */
 int sd_launch_count(sd_ctx* ctx, uint64_t* out);
+/* Device-time span over ALL of the context's streams: begin = wait until idle, record an event;
+ * end = join the streams, record an event, wait, return the elapsed milliseconds (CUDA events). */
+int sd_span_begin(sd_ctx* ctx);
+int sd_span_end(sd_ctx* ctx, double* ms);
 /* Per-kernel device timing (CUDA events on the launching stream). enable=1 starts collecting. */
 int sd_timing_enable(sd_ctx* ctx, int enable);
 /* names: "grad", "search", "intra", "grow", "inter", "points"; returns accumulated ms and launches */

@@ -7,6 +7,8 @@
 // here.  This header restates, in plain C++, the arithmetic that OpenCV performs for exactly the
 // expression shapes PM.cc uses:
 //
+//   * cv::gemm for CV_32F goes through cv::hal::gemm32f(..., float alpha, ..., float beta, ...)
+//     (OpenCV >= 3.2): alpha and beta are ROUNDED TO FLOAT first, then widened to double again.
 //   * cv::gemm "small matrix" path (modules/core/src/matmul.cpp, `flags == 0 && 2 <= len <= 4 &&
 //     (len == d_size.width || len == d_size.height)`): float products summed left to right in
 //     float, epilogue `(float)(t*alpha + c*beta)` evaluated in double.
@@ -40,6 +42,8 @@ struct V4  { float v[4]; };
 // ---- cv::gemm small path, 3x3 * 3x1 (+ optional C):  d_i = (float)(t_i*alpha + c_i*beta)
 static inline V3 gemm_small_33x31(const M33& A, const V3& b, double alpha, const V3* c, double beta) {
     V3 d;
+    alpha = (double)(float)alpha;  // hal::gemm32f takes float alpha / beta
+    beta = (double)(float)beta;
     for (int i = 0; i < 3; ++i) {
         float t = A.m[3 * i + 0] * b.v[0] + A.m[3 * i + 1] * b.v[1] + A.m[3 * i + 2] * b.v[2];
         float ci = c ? c->v[i] : 0.0f;
@@ -52,6 +56,7 @@ static inline V3 gemm_small_33x31(const M33& A, const V3& b, double alpha, const
 // ---- cv::gemm small path, 3x3 * 3x3
 static inline M33 gemm_small_33x33(const M33& A, const M33& B, double alpha) {
     M33 D;
+    alpha = (double)(float)alpha;
     for (int i = 0; i < 3; ++i)
         for (int j = 0; j < 3; ++j) {
             float t = A.m[3 * i + 0] * B.m[0 + j] + A.m[3 * i + 1] * B.m[3 + j] + A.m[3 * i + 2] * B.m[6 + j];
@@ -73,6 +78,7 @@ static inline V4 gemm_small_44x41(const M44& A, const V4& b) {
 // ---- cv::gemm general path with GEMM_2_T: D = alpha * A * B^T, double accumulation
 static inline M33 gemm_acc64_ABt(const M33& A, const M33& B, double alpha) {
     M33 D;
+    alpha = (double)(float)alpha;
     for (int i = 0; i < 3; ++i)
         for (int j = 0; j < 3; ++j) {
             double s = 0;
@@ -84,6 +90,7 @@ static inline M33 gemm_acc64_ABt(const M33& A, const M33& B, double alpha) {
 
 // ---- cv::gemm general path, 1xn * nx1 -> scalar, double accumulation, (float)(s*alpha)
 static inline float gemm_acc64_dot(const float* a, const float* b, int n, double alpha) {
+    alpha = (double)(float)alpha;
     double s = 0;
     for (int k = 0; k < n; ++k) s += (double)a[k] * (double)b[k];
     return (float)(s * alpha);

@@ -583,7 +583,8 @@ static void InterKeyFrameDepthChecking(Oracle& O, KeyFrame& cur, const std::vect
                 const KeyFrame* pKFj = neighbors[j];
                 M33 K = Kmat(pKFj->fx, pKFj->fy, pKFj->cx, pKFj->cy);
                 V3 xp = {{(px - cx) / fx, (py - cy) / fy, 1.0f}};
-                // temp = Rji*xp/depthp + tji  ->  gemm(Rji, xp, 1./depthp, tji, 1)   (operator/(MatExpr,double) multiplies alpha by 1./s)
+                // temp = Rji*xp/depthp + tji  ->  gemm(Rji, xp, 1./depthp, tji, 1)   (operator/(MatExpr,double) multiplies alpha by 1./s;
+                // hal::gemm32f then rounds that alpha to float -- inside gemm_small_33x31)
                 V3 temp = cvl::gemm_small_33x31(Rji[j], xp, 1. / (double)depthp, &tji[j], 1.0);
                 V3 Xj = cvl::gemm_small_33x31(K, temp, 1.0, nullptr, 0.0);
                 // Xj = Xj/Xj(2)  ->  convertTo(alpha = 1./s): float multiply by (float)alpha

@@ -68,6 +68,8 @@ SYMBOLS = {
     "sd_last_error": (C.c_char_p, [_vp]),
     "sd_compute_stream": (C.c_int, [_vp, C.POINTER(_vp)]),
     "sd_launch_count": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "sd_span_begin": (C.c_int, [_vp]),
+    "sd_span_end": (C.c_int, [_vp, C.POINTER(C.c_double)]),
     "sd_timing_enable": (C.c_int, [_vp, C.c_int]),
     "sd_timing_get": (C.c_int, [_vp, C.c_char_p, C.POINTER(C.c_double), C.POINTER(C.c_uint64)]),
     "sd_timing_reset": (C.c_int, [_vp]),
@@ -247,6 +249,14 @@ class Context:
         v = C.c_uint64()
         self._ck(self.L.sd_launch_count(self.h, C.byref(v)))
         return v.value
+
+    def span_begin(self):
+        self._ck(self.L.sd_span_begin(self.h))
+
+    def span_end(self):
+        ms = C.c_double()
+        self._ck(self.L.sd_span_end(self.h, C.byref(ms)))
+        return ms.value
 
     def timing_enable(self, on=True):
         self._ck(self.L.sd_timing_enable(self.h, 1 if on else 0))

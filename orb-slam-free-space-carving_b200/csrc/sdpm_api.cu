@@ -51,7 +51,7 @@ struct sd_ctx {
     SdParams P;
     int W = 0, H = 0, pitch_f = 0, pitch_u8 = 0;
     cudaStream_t s_up = nullptr, s_main = nullptr, s_dn = nullptr;
-    cudaEvent_t ev_tmp = nullptr;
+    cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
     float *tmp_depth = nullptr, *tmp_sigma = nullptr;
@@ -291,7 +291,8 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
     if (cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_dn, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&c->ev_tmp, cudaEventDisableTiming) != cudaSuccess) {
+        cudaEventCreateWithFlags(&c->ev_tmp, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreate(&c->ev_span_a) != cudaSuccess || cudaEventCreate(&c->ev_span_b) != cudaSuccess) {
         delete c;
         return SD_ERR_CUDA;
     }
@@ -310,6 +311,8 @@ int sd_destroy(sd_ctx* c) {
     cudaFree(c->tmp_depth);
     cudaFree(c->tmp_sigma);
     if (c->ev_tmp) cudaEventDestroy(c->ev_tmp);
+    if (c->ev_span_a) cudaEventDestroy(c->ev_span_a);
+    if (c->ev_span_b) cudaEventDestroy(c->ev_span_b);
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_main);
     cudaStreamDestroy(c->s_dn);
@@ -595,6 +598,32 @@ int sd_compute_stream(sd_ctx* c, void** stream) {
 int sd_launch_count(sd_ctx* c, uint64_t* out) {
     if (!c || !out) return SD_ERR_INVALID_ARG;
     *out = c->launches;
+    return SD_OK;
+}
+
+int sd_span_begin(sd_ctx* c) {
+    int rc = sd_sync(c);
+    if (rc != SD_OK) return rc;
+    CU(c, cudaEventRecord(c->ev_span_a, c->s_main));
+    // later work on the other two streams must not start before the span does
+    CU(c, cudaStreamWaitEvent(c->s_up, c->ev_span_a, 0));
+    CU(c, cudaStreamWaitEvent(c->s_dn, c->ev_span_a, 0));
+    return SD_OK;
+}
+
+int sd_span_end(sd_ctx* c, double* ms) {
+    if (!c || !ms) return SD_ERR_INVALID_ARG;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaEventRecord(c->ev_tmp, c->s_up));
+    CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
+    CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
+    CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
+    CU(c, cudaEventRecord(c->ev_span_b, c->s_main));
+    int rc = sd_sync(c);
+    if (rc != SD_OK) return rc;
+    float f = 0;
+    CU(c, cudaEventElapsedTime(&f, c->ev_span_a, c->ev_span_b));
+    *ms = f;
     return SD_OK;
 }
 

@@ -614,7 +614,8 @@ __global__ void __launch_bounds__(256) k4_inter_check(const __grid_constant__ In
     if (px >= 2 && px < A.W - 2 && py >= 2 && py < A.H - 2 && depthp > SD_EPS_F) {  // PM.cc:659-662 (`< 1e-6 -> continue`)
         const float xp0 = ((float)px - A.cx) / A.fx, xp1 = ((float)py - A.cy) / A.fy;
         const float dp = 1 / depthp;
-        const double inv_dp = 1.0 / (double)depthp;  // operator/(MatExpr, double): alpha = 1./s
+        // operator/(MatExpr, double): alpha = 1./s, which hal::gemm32f(float alpha) rounds to float
+        const double inv_dp = (double)(float)(1.0 / (double)depthp);
         int nkf = 0;
         double sJr = 0.0, sJJ = 0.0;
         for (int j = 0; j < A.n; ++j) {
