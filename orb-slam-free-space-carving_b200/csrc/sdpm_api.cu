@@ -29,7 +29,8 @@ struct Slot {
     float Rcw[9], tcw[3], Twc[16];
     uint8_t* slab = nullptr;  // one allocation for everything below except points
     uint8_t* gray = nullptr;
-    float *grad = nullptr, *theta = nullptr, *gate = nullptr, *depth = nullptr, *sigma = nullptr, *depth_chk = nullptr;
+    float *grad = nullptr, *theta = nullptr, *depth = nullptr, *sigma = nullptr, *depth_chk = nullptr;
+    uint32_t* arc = nullptr;  // SD_ARC_PLANES orientation-arc bit planes (k0_gradient)
     float* points = nullptr;
     uint32_t* list = nullptr;
     KfMeta* meta = nullptr;
@@ -49,7 +50,7 @@ struct TimedSpan {
 struct sd_ctx {
     int device = 0;
     SdParams P;
-    int W = 0, H = 0, pitch_f = 0, pitch_u8 = 0;
+    int W = 0, H = 0, pitch_f = 0, pitch_u8 = 0, arc_pitch = 0;
     cudaStream_t s_up = nullptr, s_main = nullptr, s_dn = nullptr;
     cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
@@ -63,6 +64,7 @@ struct sd_ctx {
     double t_ms[T_COUNT] = {0};
     uint64_t t_n[T_COUNT] = {0};
     float chi_fuse_f = 0, chi_inter_f = 0;
+    int sm_count = 0, k1_grid = 0;  // persistent k1_search grid: SMs x resident blocks
 };
 
 namespace {
@@ -100,7 +102,8 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     const size_t fplane = align_up((size_t)c->pitch_f * c->H * sizeof(float), 256);
     const size_t uplane = align_up((size_t)c->pitch_u8 * c->H, 256);
     const size_t lplane = align_up((size_t)c->W * c->H * sizeof(uint32_t), 256);
-    const size_t total = uplane + 6 * fplane + lplane + 256;
+    const size_t aplane = align_up((size_t)SD_ARC_PLANES * c->H * c->arc_pitch * sizeof(uint32_t), 256);
+    const size_t total = uplane + 5 * fplane + aplane + lplane + 256;
     cudaError_t e = cudaMalloc(&s->slab, total);
     if (e != cudaSuccess) {
         delete s;
@@ -110,7 +113,7 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->gray = p; p += uplane;
     s->grad = (float*)p; p += fplane;
     s->theta = (float*)p; p += fplane;
-    s->gate = (float*)p; p += fplane;
+    s->arc = (uint32_t*)p; p += aplane;
     s->depth = (float*)p; p += fplane;
     s->sigma = (float*)p; p += fplane;
     s->depth_chk = (float*)p; p += fplane;
@@ -186,7 +189,8 @@ void set_pose_fields(Slot* s, const float Tcw[12]) {
 
 int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int w, int h, int stride, const float K[4],
                   const float Tcw[12]) {
-    if (!c || !gray || !K || !Tcw || w < 8 || h < 8 || stride < w || w > 65535 || h > 65535)
+    if (!c || !gray || !K || !Tcw || w < 8 || h < 8 || stride < w || w > 65535 || h > 65535 ||
+        (long long)(w + 128) * h >= (1ll << 30))  // kernels index planes with 32-bit element offsets
         return fail(c, SD_ERR_INVALID_ARG, "sd_upload_keyframe: bad argument");
     CU(c, cudaSetDevice(c->device));
     if (c->W == 0) {
@@ -194,6 +198,7 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         c->H = h;
         c->pitch_f = (int)align_up(w, 32);
         c->pitch_u8 = (int)align_up(w, 128);
+        c->arc_pitch = 4 * ((w + K0_TW - 1) / K0_TW);  // u32 words per bit-plane row, whole K0 tiles
         const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
         CU(c, cudaMalloc(&c->tmp_depth, fplane));
         CU(c, cudaMalloc(&c->tmp_sigma, fplane));
@@ -223,8 +228,8 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
     {
         ScopedTimer t(c, c->s_up, T_GRAD);
         dim3 blk(K0_TX, K0_TY), grd((w + K0_TW - 1) / K0_TW, (h + K0_TY - 1) / K0_TY);
-        k0_gradient<<<grd, blk, 0, c->s_up>>>(s->gray, c->pitch_u8, w, h, s->grad, s->theta, s->gate, c->pitch_f, s->list, s->meta,
-                                              c->P.lambdaG, c->P.border);
+        k0_gradient<<<grd, blk, 0, c->s_up>>>(s->gray, c->pitch_u8, w, h, s->grad, s->theta, c->pitch_f, s->arc, c->arc_pitch,
+                                              s->list, s->meta, c->P.lambdaG, c->P.lambdaTheta, c->P.border);
     }
     k0_finalize<<<1, 1, 0, c->s_up>>>(s->meta, w, h);
     c->launches++;
@@ -234,16 +239,17 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
 }
 
 void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
-    A.W = c->W; A.H = c->H; A.pitch_f = c->pitch_f; A.pitch_u8 = c->pitch_u8;
-    A.border = c->P.border; A.lambdaN = c->P.lambdaN;
+    A.W = c->W; A.H = c->H; A.pitch_f = c->pitch_f; A.pitch_u8 = c->pitch_u8; A.arc_pitch = c->arc_pitch;
+    A.border = c->P.border; A.lambdaN = c->P.lambdaN; A.lambdaG = c->P.lambdaG;
     A.fx = s->K[0]; A.fy = s->K[1]; A.cx = s->K[2]; A.cy = s->K[3];
     A.lambdaL = c->P.lambdaL; A.lambdaTheta = c->P.lambdaTheta; A.slope = c->P.slope_limit;
     A.chi_fuse = c->chi_fuse_f;
     A.THETA = c->P.theta;
     A.inv_THETA = 1 / c->P.theta;
-    A.img = s->gray; A.grad = s->grad; A.gate = s->gate; A.theta = s->theta;
+    A.img = s->gray; A.grad = s->grad; A.theta = s->theta;
     A.list = s->list; A.meta = s->meta;
     A.count_override = -1;
+    A.task_counter = &s->meta->k1_task;
     A.depth = s->depth; A.sigma = s->sigma;
     A.probe_out = nullptr;
 }
@@ -252,7 +258,7 @@ void fill_nbr(Slot* s, Slot* nb, float rot, NbrConst& N) {
     geom::fundamental(s->K, s->Rcw, s->tcw, nb->K, nb->Rcw, nb->tcw, N.F);
     geom::relative_pose(s->Rcw, s->tcw, nb->Rcw, nb->tcw, N.R, N.t);
     N.rot = rot;
-    N.img = nb->gray; N.grad = nb->grad; N.gate = nb->gate; N.meta = nb->meta;
+    N.img = nb->gray; N.grad = nb->grad; N.theta = nb->theta; N.arc = nb->arc; N.meta = nb->meta;
 }
 
 }  // namespace
@@ -282,7 +288,7 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
     sd_ctx* c = new sd_ctx();
     c->device = device;
     if (params) c->P = *params; else sd_default_params(&c->P);
-    if (c->P.border < 1 || c->P.lambdaN < 1 || !(c->P.theta > 0)) {
+    if (c->P.border < 1 || c->P.lambdaN < 1 || !(c->P.theta > 0) || !(c->P.lambdaTheta >= 0) || !(c->P.lambdaL >= 0)) {
         delete c;
         return SD_ERR_INVALID_ARG;
     }
@@ -295,6 +301,17 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
         cudaEventCreate(&c->ev_span_a) != cudaSuccess || cudaEventCreate(&c->ev_span_b) != cudaSuccess) {
         delete c;
         return SD_ERR_CUDA;
+    }
+    {
+        cudaDeviceProp prop;
+        int per_sm = 0;
+        if (cudaGetDeviceProperties(&prop, device) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k1_search, K1_WARPS * 32, 0) != cudaSuccess || per_sm < 1) {
+            delete c;
+            return SD_ERR_CUDA;
+        }
+        c->sm_count = prop.multiProcessorCount;
+        c->k1_grid = c->sm_count * per_sm;
     }
     *out = c;
     return SD_OK;
@@ -373,11 +390,10 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
     CU(c, cudaMemsetAsync(s->depth, 0, fplane, c->s_main));
     CU(c, cudaMemsetAsync(s->sigma, 0, fplane, c->s_main));
+    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), c->s_main));
     {
         ScopedTimer t(c, c->s_main, T_SEARCH);
-        const int max_entries = c->W * c->H;
-        const int blocks = (max_entries + K1_WARPS * 32 - 1) / (K1_WARPS * 32);
-        k1_search<<<blocks, K1_WARPS * 32, 0, c->s_main>>>(A);
+        k1_search<<<c->k1_grid, K1_WARPS * 32, 0, c->s_main>>>(A);
     }
     StencilArgs S;
     S.W = c->W; S.H = c->H; S.pitch_f = c->pitch_f; S.border = c->P.border;
@@ -730,7 +746,7 @@ int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float m
     }
     uint32_t* d_list = nullptr;
     float* d_out = nullptr;
-    CU(c, cudaMalloc(&d_list, n * sizeof(uint32_t)));
+    CU(c, cudaMalloc(&d_list, (n + 1) * sizeof(uint32_t)));  // + the task counter
     CU(c, cudaMalloc(&d_out, (size_t)n * 4 * sizeof(float)));
     CU(c, cudaStreamSynchronize(c->s_up));
     CU(c, cudaMemcpyAsync(d_list, entries.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, c->s_main));
@@ -741,9 +757,11 @@ int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float m
     A.maxd = max_invdepth;
     A.list = d_list;
     A.count_override = n;
+    A.task_counter = d_list + n;
+    CU(c, cudaMemsetAsync(d_list + n, 0, sizeof(uint32_t), c->s_main));
     A.probe_out = d_out;
     fill_nbr(s, nb, rot_deg, A.nb[0]);
-    const int blocks = (n + K1_WARPS * 32 - 1) / (K1_WARPS * 32);
+    const int blocks = std::min(c->k1_grid, (n + K1_WARPS * 32 - 1) / (K1_WARPS * 32));
     k1_search<<<blocks, K1_WARPS * 32, 0, c->s_main>>>(A);
     c->launches++;
     CU(c, cudaGetLastError());

@@ -1,6 +1,6 @@
 // CUDA kernels (sm_100a) of the semi-dense probability-mapping path.
 //
-//   K0 k0_gradient     image -> GradImg / GradTheta / gate plane / active-pixel list / I_stddev sums
+//   K0 k0_gradient     image -> GradImg / GradTheta / orientation-arc bit planes / active-pixel list / I_stddev sums
 //   K1 k1_search       per active pixel: EpipolarSearch in N neighbours + InverseDepthHypothesisFusion
 //   K2 k2_intra_check  IntraKeyFrameDepthChecking           (3x3 chi-square stencil)
 //   K3 k3_intra_grow   IntraKeyFrameDepthGrowing            (3x3 chi-square stencil)
@@ -30,6 +30,8 @@ struct KfMeta {  // device-resident per key frame
     unsigned long long sumsq;  // sum of squared grey levels
     float istddev;             // KeyFrame::I_stddev
     int active_count;          // entries in the active-pixel list
+    unsigned int k1_task;      // next 32-entry task of the running k1_search launch (zeroed before each launch)
+    unsigned int pad_;
 };
 
 struct NbrConst {  // per neighbour, warp-uniform, lives in kernel parameter (constant) space
@@ -39,25 +41,27 @@ struct NbrConst {  // per neighbour, warp-uniform, lives in kernel parameter (co
     float rot;     // median in-plane rotation, degrees, PM.cc:170-179
     const uint8_t* img;
     const float* grad;
-    const float* gate;  // GradTheta where GradImg >= lambdaG, else -1
+    const float* theta;
+    const uint32_t* arc;  // SD_ARC_PLANES bit planes, see k0_gradient
     const KfMeta* meta;
 };
 
 struct SearchArgs {
     int W, H, pitch_f, pitch_u8, n;
+    int arc_pitch;  // u32 words per bit-plane row
     int border, lambdaN;
     float fx, fy, cx, cy;
     float mind, maxd;  // StereoSearchConstraints interval (inverse depth; mind is the larger), PM.cc:381-382
-    float lambdaL, lambdaTheta, slope;
+    float lambdaG, lambdaL, lambdaTheta, slope;
     float chi_fuse;  // smallest float >= 5.99: `chi < 5.99` (float vs double literal) == `chi < chi_fuse`
     double inv_THETA, THETA;  // 1/THETA and THETA (PM.h:47) as doubles
     const uint8_t* img;
     const float* grad;
-    const float* gate;
     const float* theta;
     const uint32_t* list;
     const KfMeta* meta;
     int count_override;  // >= 0: use instead of meta->active_count (probes)
+    unsigned int* task_counter;  // zeroed before the launch; warps draw 32-entry tasks from it
     float* depth;
     float* sigma;
     float* probe_out;  // nullable; [entry][4] = {rho, sigma, best uj, supported} of neighbour 0
@@ -128,19 +132,36 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// K0: gradient front end (build-defined) + active list + I_stddev sums.
-// 3x3 Sobel/8 with replicate border; GradImg = sqrtf(gx^2+gy^2); GradTheta = fastAtan2(gy,gx);
-// gate = GradImg >= lambdaG ? GradTheta : -1.  Block 32x8 threads, 4 pixels per thread (128x8 tile).
+// K0: gradient front end (build-defined) + orientation-arc bit planes + active list +
+// I_stddev sums.
+// 3x3 Sobel/8 with replicate border; GradImg = sqrtf(gx^2+gy^2); GradTheta = fastAtan2(gy,gx).
+// Block 32x8 threads, 4 pixels per thread (128x8 tile).
+//
+// Orientation-arc bit planes (what K1 scans instead of testing every candidate column):
+// plane s (s = 0..31) holds one bit per pixel, row-major, 32 columns per u32 word (bit = x & 31):
+//     bit = GradImg >= lambdaG  (condition 1, PM.cc:411)
+//           && circular distance(GradTheta, (s + 0.5) * 11.25 deg) <= lambdaTheta + 5.625 + SD_ARC_MARGIN
+// i.e. every pixel that condition 3 (PM.cc:424-431) can accept for SOME rotated orientation
+// `th_pi + rot` inside the 11.25-degree cell s.  It is a conservative SUPERSET: K1 re-runs the
+// exact float tests of conditions 2 and 3 on every pixel a plane selects, so the planes only
+// decide which columns are looked at, never the result.  Plane 32 is condition 1 alone (used when
+// the rotated orientation falls outside [0, 360), where PM.cc's single fold is not a circular
+// distance).  All 33 planes together are 33/8 bytes per pixel.
 // ------------------------------------------------------------------------------------------------
 constexpr int K0_TX = 32, K0_TY = 8, K0_PX = 4;
 constexpr int K0_TW = K0_TX * K0_PX;  // 128
+constexpr int SD_ARC_CELLS = 32;
+constexpr int SD_ARC_PLANES = SD_ARC_CELLS + 1;
+#define SD_ARC_CELL_DEG 11.25f
+#define SD_ARC_MARGIN 0.05f
 
 __global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __restrict__ img, int pitch_u8, int W, int H,
-                                                            float* __restrict__ grad, float* __restrict__ theta,
-                                                            float* __restrict__ gate, int pitch_f,
+                                                            float* __restrict__ grad, float* __restrict__ theta, int pitch_f,
+                                                            uint32_t* __restrict__ arc, int arc_pitch,
                                                             uint32_t* __restrict__ list, KfMeta* __restrict__ meta,
-                                                            float lambdaG, int border) {
+                                                            float lambdaG, float lambdaTheta, int border) {
     __shared__ uint8_t tile[K0_TY + 2][K0_TW + 8];  // column c <-> x0 - 1 + c
+    __shared__ uint32_t s_memb[K0_TY][K0_TW];        // per pixel: bit s = member of arc plane s
     __shared__ int warp_cnt[K0_TY];
     __shared__ int block_base;
     __shared__ unsigned long long red[2][K0_TY];
@@ -158,7 +179,8 @@ __global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __res
 
     const int y = y0 + ty;
     const int xb = x0 + tx * K0_PX;
-    float g[K0_PX], th[K0_PX], gt[K0_PX];
+    const float arcR = lambdaTheta + 0.5f * SD_ARC_CELL_DEG + SD_ARC_MARGIN;
+    float g[K0_PX], th[K0_PX];
     unsigned long long s1 = 0, s2 = 0;
     uint32_t act[K0_PX];
     int nact = 0;
@@ -173,9 +195,19 @@ __global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __res
         float gx = (float)sx * 0.125f, gy = (float)sy * 0.125f;
         g[i] = sqrtf(gx * gx + gy * gy);
         th[i] = fast_atan2_deg(gy, gx);
-        const bool on = g[i] >= lambdaG;
-        gt[i] = on ? th[i] : -1.0f;
         const int x = xb + i;
+        const bool on = (g[i] >= lambdaG) && x < W && y < H;
+        uint32_t memb = 0;
+        if (on) {
+            // cells s (mod 32) with (s + 0.5) * cell within arcR of theta
+            const float lo = (th[i] - arcR) * (1.0f / SD_ARC_CELL_DEG) - 0.5f;
+            const float hi = (th[i] + arcR) * (1.0f / SD_ARC_CELL_DEG) - 0.5f;
+            const int s_lo = (int)ceilf(lo), s_hi = (int)floorf(hi);
+            const int cnt = s_hi - s_lo + 1;
+            if (cnt >= SD_ARC_CELLS) memb = 0xffffffffu;
+            else if (cnt > 0) memb = __funnelshift_l((1u << cnt) - 1u, (1u << cnt) - 1u, s_lo & 31);  // rotate left
+        }
+        s_memb[ty][tx * K0_PX + i] = memb;
         if (x < W && y < H) {
             s1 += (unsigned)p11;
             s2 += (unsigned)(p11 * p11);
@@ -187,15 +219,40 @@ __global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __res
         if (xb + K0_PX <= W) {  // pitch_f and xb are multiples of 4: aligned float4 stores
             *reinterpret_cast<float4*>(grad + o) = make_float4(g[0], g[1], g[2], g[3]);
             *reinterpret_cast<float4*>(theta + o) = make_float4(th[0], th[1], th[2], th[3]);
-            *reinterpret_cast<float4*>(gate + o) = make_float4(gt[0], gt[1], gt[2], gt[3]);
         } else {
             for (int i = 0; i < K0_PX; ++i)
-                if (xb + i < W) { grad[o + i] = g[i]; theta[o + i] = th[i]; gate[o + i] = gt[i]; }
+                if (xb + i < W) { grad[o + i] = g[i]; theta[o + i] = th[i]; }
+        }
+    }
+
+    // 128 pixels x 32 planes -> 32 planes x 4 words: the warp (one image row of the tile) transposes
+    // its membership words with ballots; lane s ends up with the 4 words of plane s.
+    __syncwarp();
+    const unsigned full = 0xffffffffu;
+    uint32_t pw[K0_PX], pall[K0_PX];
+#pragma unroll
+    for (int w = 0; w < K0_PX; ++w) {
+        const uint32_t v = s_memb[ty][w * 32 + tx];
+        uint32_t mine = 0;
+#pragma unroll
+        for (int s = 0; s < SD_ARC_CELLS; ++s) {
+            const uint32_t b = __ballot_sync(full, (v >> s) & 1u);
+            if (tx == s) mine = b;
+        }
+        pw[w] = mine;
+        pall[w] = __ballot_sync(full, v != 0u);
+    }
+    if (y < H) {  // arc_pitch is a multiple of 4 words and covers the last tile: aligned uint4 stores
+        const size_t plane = (size_t)H * arc_pitch;
+        uint32_t* dst = arc + (size_t)tx * plane + (size_t)y * arc_pitch + (x0 >> 5);
+        *reinterpret_cast<uint4*>(dst) = make_uint4(pw[0], pw[1], pw[2], pw[3]);
+        if (tx == 0) {
+            uint32_t* d32 = arc + (size_t)SD_ARC_CELLS * plane + (size_t)y * arc_pitch + (x0 >> 5);
+            *reinterpret_cast<uint4*>(d32) = make_uint4(pall[0], pall[1], pall[2], pall[3]);
         }
     }
 
     // block-wide compaction of the active pixels: warp scan, then one atomicAdd per block
-    const unsigned full = 0xffffffffu;
     int incl = nact;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -273,32 +330,168 @@ __device__ __forceinline__ bool chi_test(float a, float b, float sa, float sb, f
     return chi < thr;
 }
 
+// conditions 2 and 3 of EpipolarSearch on one candidate orientation T2 (degrees), PM.cc:414-431
+__device__ __forceinline__ bool orientation_gates(float T2, float th_epi, float apr, float lambdaL, float lambdaTheta) {
+    float d = T2 - th_epi;  // condition 2, PM.cc:414-421
+    if (d >= 360) d -= 360;
+    if (d < 0) d += 360;
+    if (d > 180) d = 360 - d;
+    if (d > 90) d = 180 - d;
+    float e = T2 - apr;  // condition 3, PM.cc:427-431
+    if (e >= 360) e -= 360;
+    if (e < 0) e += 360;
+    if (e > 180) e = 360 - e;
+    return !(d > lambdaL) && !(e > lambdaTheta);
+}
+
+// row index of candidate column u on the epipolar line: vj = -(int)((a/b)*uj + c/b), PM.cc:407.
+// Returns ti = -vj.  Rounding is monotone, so ti is monotone in u: the columns that share a row are
+// one contiguous run.  (__float2int_rz saturates; NaN -> 0, which is an invalid row.)
+__device__ __forceinline__ int line_row_neg(float ab, float cb, int u) {
+    return __float2int_rz(__fadd_rn(__fmul_rn(ab, (float)u), cb));
+}
+
+// largest u1 in [u, ue) whose row equals t0; precondition line_row_neg(u) == t0 != line_row_neg(ue).
+// The division-based estimate only decides where the exact search starts.
+__device__ __forceinline__ int run_end(float ab, float cb, float inv_ab, int u, int ue, int t0) {
+    const float bv = (float)t0 + ((ab > 0.f) ? (t0 < 0 ? 0.f : 1.f) : (t0 <= 0 ? -1.f : 0.f));
+    const float uc = (bv - cb) * inv_ab;
+    int u1 = (uc >= (float)u) ? ((uc < (float)ue) ? (int)uc : ue - 1) : u;  // NaN -> u
+    while (u1 > u && line_row_neg(ab, cb, u1) != t0) --u1;
+    while (u1 + 1 < ue && line_row_neg(ab, cb, u1 + 1) == t0) ++u1;
+    return u1;
+}
+
+struct LineScan {  // what the sequential reference scan of one epipolar line needs
+    float ab, cb, I1, g1, th_epi, apr;
+    int u_lo, u_hi;
+};
+
+// The reference's own loop, PM.cc:405-444, candidate by candidate with the exact arithmetic
+// (err in double because THETA is a double literal).  Used only for the rare pixels whose two best
+// matches are closer than the float shortcut of the fast path can separate.  Returns best uj or -1.
+__device__ __noinline__ int exact_line_scan(const SearchArgs& A, const NbrConst& N, const LineScan& L) {
+    float best = 1000000.0f;
+    int bj = -1;
+    for (int uj = L.u_lo; uj <= L.u_hi; ++uj) {
+        const int ti = line_row_neg(L.ab, L.cb, uj);
+        if (!(ti < 0 && ti > -A.H)) continue;  // PM.cc:408
+        const size_t o = (size_t)(-ti) * A.pitch_f + min(uj, A.W - 1);
+        if (__ldg(N.grad + o) < A.lambdaG) continue;  // PM.cc:411
+        if (!orientation_gates(__ldg(N.theta + o), L.th_epi, L.apr, A.lambdaL, A.lambdaTheta)) continue;
+        const float yv = -(L.ab * (float)uj + L.cb);
+        const float rI = L.I1 - bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yv, uj);
+        const float rG = L.g1 - bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yv, uj);
+        const float err = (float)((double)(rI * rI) + (double)(rG * rG) / A.THETA);  // PM.cc:436
+        if (err < best) { best = err; bj = uj; }                                      // PM.cc:437-443
+    }
+    return bj;
+}
+
+// ChiTest decided without a division whenever the answer is not within 1e-5 of the threshold:
+// q = sigma^2 (float product, as in PM.cc:920-921), r = 1/q.  num*ra + num*rb differs from the
+// reference's num/qa + num/qb by < 3e-7 relative, so outside the guard band both give the same
+// answer; inside it (or for NaN / inf intermediates) the reference expression itself is evaluated.
+__device__ __forceinline__ bool chi_test_q(float a, float b, float qa, float qb, float ra, float rb, float thr, float thr_lo, float thr_hi) {
+    const float dl = a - b;
+    const float num = dl * dl;
+    const float approx = num * ra + num * rb;
+    if (approx < thr_lo) return true;
+    if (approx > thr_hi) return false;
+    return num / qa + num / qb < thr;
+}
+
+// InverseDepthHypothesisFusion, PM.cc:598-626 (+ ChiTest 912-924, GetFusion 947-970) on the nh
+// hypotheses of one pixel.  ChiTest is symmetric in (a, b) (the squared difference and the float
+// sum commute), so each unordered pair is tested once.  Returns false when unsupported.
+__device__ __forceinline__ bool fuse_hypotheses(const float* hd, const float* hs, int nh, int lambdaN, float thr, float& out_d, float& out_s) {
+    float hq[SD_MAX_NEIGHBOURS], hr[SD_MAX_NEIGHBOURS];
+    unsigned char cnt[SD_MAX_NEIGHBOURS];
+    const float thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
+    for (int i = 0; i < nh; ++i) {
+        const float q = hs[i] * hs[i];
+        hq[i] = q;
+        hr[i] = 1.0f / q;
+        // ChiTest(a, a): num = +0, chi = 0/q + 0/q = 0 unless q is 0 or NaN (then NaN -> false)
+        cnt[i] = (q > 0.0f && 0.0f < thr) ? 1 : 0;
+    }
+    for (int i = 0; i < nh; ++i) {
+        const float di = hd[i], qi = hq[i], ri = hr[i];
+        int ci = 0;
+        for (int k = i + 1; k < nh; ++k) {
+            if (chi_test_q(di, hd[k], qi, hq[k], ri, hr[k], thr, thr_lo, thr_hi)) {
+                ++ci;
+                cnt[k] = (unsigned char)(cnt[k] + 1);
+            }
+        }
+        cnt[i] = (unsigned char)(cnt[i] + ci);
+    }
+    int best_cnt = 0, best_a = -1;
+    for (int i = 0; i < nh; ++i)
+        if ((int)cnt[i] > best_cnt) { best_cnt = cnt[i]; best_a = i; }  // strict >, first largest set wins (PM.cc:616)
+    if (best_cnt < lambdaN) return false;
+    // GetFusion(depthHo), PM.cc:947-970: pow(sigma,2) in double, float accumulators, members in index order
+    float pjsj = 0, rsj = 0;
+    const float da = hd[best_a], qa = hq[best_a], ra = hr[best_a];
+    for (int ib = 0; ib < nh; ++ib) {
+        const bool comp = (ib == best_a) ? (qa > 0.0f && 0.0f < thr) : chi_test_q(da, hd[ib], qa, hq[ib], ra, hr[ib], thr, thr_lo, thr_hi);
+        if (!comp) continue;
+        const double s2 = (double)hs[ib] * (double)hs[ib];
+        pjsj = (float)((double)pjsj + (double)hd[ib] / s2);
+        rsj = (float)((double)rsj + 1.0 / s2);
+    }
+    out_d = pjsj / rsj;
+    out_s = sqrtf(1 / rsj);
+    return true;
+}
+
 constexpr int K1_WARPS = 8;
-constexpr int K1_QCAP = 64;
+constexpr int K1_QCAP = 1024 + 32;  // one scan step queues at most 32 lanes x 32 columns on top of < 32 leftovers
+#define K1_TIE_REL 2e-6f            // float shortcut of err: two candidates closer than this are re-scanned exactly
+#define K1_ERR_LIMIT_LO 999000.0f   // PM.cc:437 initial best_match_err = 1e6
 
 // One warp = 32 consecutive entries of the active-pixel list (one lane per pixel).  For each
-// neighbour key frame: (A) per lane the epipolar line, slope test, search range and the two
-// gate angles; (B) all lanes walk their own candidate columns, the three cheap gates
-// (PM.cc:408-431) run on every candidate from ONE gathered float (the gate plane), survivors are
-// pushed into a per-warp shared-memory queue; (C) whenever 32 survivors are queued they are
-// evaluated one per lane (photometric + gradient residual, PM.cc:433-436) and merged into the
-// owner's best match with a 64-bit shared atomicMin on (err bits, uj) -- smallest err wins, ties
-// go to the smallest uj, exactly the sequential strict-< scan of PM.cc:437-443; (D) per lane the
-// sub-pixel refinement and the inverse-depth hypothesis (PM.cc:446-463, 806-829).  After the last
-// neighbour: InverseDepthHypothesisFusion (PM.cc:598-626) per lane.
+// neighbour key frame:
+//  (A) per lane: epipolar line, slope test, search range, the two gate angles (PM.cc:389-404, 414,
+//      424-426) and the orientation-arc plane of the neighbour that matches `th_pi + rot`.
+//  (B) per lane: walk the line run by run (a run = consecutive columns on one image row, clipped to
+//      a 32-column word of the bit plane): ONE u32 load yields every column of the run that passes
+//      condition 1 and can pass condition 3.  Selected columns are pushed to a per-warp queue.
+//  (C) whenever 32 are queued they are evaluated one per lane, whichever lane they came from: exact
+//      conditions 2+3 on GradTheta, photometric + gradient residual (PM.cc:433-436) with the err
+//      of PM.cc:436 in float; shared-memory atomicMin keeps the smallest err per owner.  A pixel
+//      whose two smallest errs are within K1_TIE_REL of each other is flagged and re-scanned by
+//      exact_line_scan, so the winner is always the one the reference's sequential strict-<
+//      scan picks (smallest err in the reference arithmetic, first column on ties).
+//  (D) per lane: sub-pixel refinement and inverse-depth hypothesis (PM.cc:446-463, 806-829).
+// After the last neighbour: InverseDepthHypothesisFusion (PM.cc:598-626) per lane.
 __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant__ SearchArgs A) {
     __shared__ uint32_t s_queue[K1_WARPS][K1_QCAP];
-    __shared__ unsigned long long s_best[K1_WARPS][32];
+    __shared__ uint32_t s_beste[K1_WARPS][32];
+    __shared__ uint32_t s_bestu[K1_WARPS][32];
+    __shared__ uint32_t s_qn[K1_WARPS];
+    __shared__ uint32_t s_tie[K1_WARPS];
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int count = A.count_override >= 0 ? A.count_override : A.meta->active_count;
-    const int entry = (blockIdx.x * K1_WARPS + wib) * 32 + lane;
-    if (entry - lane >= count) return;  // whole warp out of range
-    const bool valid = entry < count;
 
     uint32_t* queue = s_queue[wib];
-    unsigned long long* best = s_best[wib];
+    uint32_t* beste = s_beste[wib];
+    uint32_t* bestu = s_bestu[wib];
+    volatile uint32_t* qn_s = &s_qn[wib];
+    const float colsf = (float)A.W;
+    const float inv_theta_f = (float)A.inv_THETA;
+    const size_t arc_plane = (size_t)A.H * A.arc_pitch;
+
+  // persistent warps: the grid is sized to the machine, every warp draws 32-entry tasks until none are left
+  for (;;) {
+    unsigned task = 0;
+    if (lane == 0) task = atomicAdd(A.task_counter, 1u);
+    task = __shfl_sync(full, task, 0);
+    if ((long long)task * 32 >= (long long)count) break;
+    const int entry = (int)task * 32 + lane;
+    const bool valid = entry < count;
 
     int x = 0, y = 0;
     if (valid) {
@@ -311,7 +504,6 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
     const float g1 = valid ? __ldg(A.grad + (size_t)y * A.pitch_f + x) : 0.f;         // PM.cc:434
     const float th1 = valid ? __ldg(A.theta + (size_t)y * A.pitch_f + x) : 0.f;       // PM.cc:214
     const float xp0 = (xf - A.cx) / A.fx, xp1 = (yf - A.cy) / A.fy;                   // PM.cc:893, 862
-    const float colsf = (float)A.W;
 
     float hd[SD_MAX_NEIGHBOURS], hs[SD_MAX_NEIGHBOURS];
     int nh = 0;
@@ -327,9 +519,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
 
         // xp2 = gemm(R21, xp1, rho, t21, 1): float dot left to right, epilogue in double
         const float q0 = N.R[0] * xp0 + N.R[1] * xp1 + N.R[2] * 1.0f;
-        const float q1 = N.R[3] * xp0 + N.R[4] * xp1 + N.R[5] * 1.0f;
         const float q2 = N.R[6] * xp0 + N.R[7] * xp1 + N.R[8] * 1.0f;
-        (void)q1;
         const float xmin0 = (float)__fma_rn((double)q0, (double)A.mind, (double)N.t[0]);
         const float xmin2 = (float)__fma_rn((double)q2, (double)A.mind, (double)N.t[2]);
         const float xmax0 = (float)__fma_rn((double)q0, (double)A.maxd, (double)N.t[0]);
@@ -343,92 +533,143 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
         if (umax > colsf) umax = colsf;
         if (!(umin == umin) || !(umax == umax)) ok = false;  // NaN bounds: empty range
         const int u_lo = (int)ceilf(umin);
-        const int u_hi = (int)floorf(umax);
-        const int cnt = ok ? max(0, u_hi - u_lo + 1) : 0;
+        const int u_hi = ok ? (int)floorf(umax) : -1;  // candidates: u_lo..u_hi (u_hi may equal W)
 
         // gate angles, loop invariant: PM.cc:414, 424-426
         const float th_epi = fast_atan2_deg(-ab, 1.0f);
         float apr = th1 + N.rot;
         if (apr >= 360) apr -= 360;
         if (apr < 0) apr += 360;
+        // arc plane of the neighbour for this rotated orientation (plane 32 = condition 1 only)
+        int cell = SD_ARC_CELLS;
+        if (apr >= 0.f && apr < 360.f) cell = min((int)(apr * (1.0f / SD_ARC_CELL_DEG)), SD_ARC_CELLS - 1);
+        const uint32_t* __restrict__ arcp = N.arc + (size_t)cell * arc_plane;
+        const float inv_ab = 1.0f / ab;
 
-        best[lane] = ~0ull;
+        beste[lane] = 0x7f800000u;  // +inf
+        if (lane == 0) { *qn_s = 0; s_tie[wib] = 0; }
         __syncwarp();
 
-        // ---------------- (B)+(C) candidate scan ----------------
-        const int maxcnt = __reduce_max_sync(full, cnt);
-        const float* __restrict__ gate2 = N.gate;
+        // ---------------- (C) evaluate queued candidates, one per lane ----------------
         int qn = 0;
-        float uf = (float)u_lo;
-        for (int it = 0; it < maxcnt; ++it, uf += 1.0f) {
-            bool surv = false;
-            const int uj = u_lo + it;
-            if (it < cnt) {
-                const float vf = ab * uf + cb;      // (a/b)*uj + (c/b), PM.cc:407
-                const int ti = __float2int_rz(vf);  // saturating; NaN -> 0.  vj = -ti
-                if (ti < 0 && ti > -A.H) {          // PM.cc:408: 0 < vj < rows
-                    const float T2 = __ldg(gate2 + (size_t)(-ti) * A.pitch_f + min(uj, A.W - 1));
-                    if (T2 >= 0.0f) {  // condition 1, PM.cc:411
-                        float d = T2 - th_epi;  // condition 2, PM.cc:414-421
-                        if (d >= 360) d -= 360;
-                        if (d < 0) d += 360;
-                        if (d > 180) d = 360 - d;
-                        if (d > 90) d = 180 - d;
-                        float e = T2 - apr;  // condition 3, PM.cc:427-431
-                        if (e >= 360) e -= 360;
-                        if (e < 0) e += 360;
-                        if (e > 180) e = 360 - e;
-                        surv = !(d > A.lambdaL) && !(e > A.lambdaTheta);
-                    }
-                }
-            }
-            const unsigned m = __ballot_sync(full, surv);
-            if (m) {
-                if (surv) queue[qn + __popc(m & ((1u << lane) - 1u))] = ((uint32_t)lane << 16) | (uint32_t)uj;
-                qn += __popc(m);
-                __syncwarp();
-            }
-            const bool last = (it == maxcnt - 1);
-            while (qn >= 32 || (last && qn > 0)) {
-                // ---------------- (C) evaluate up to 32 queued survivors, one per lane ----------------
+        auto drain = [&](bool all) {
+            while (qn >= 32 || (all && qn > 0)) {
                 const int take = min(qn, 32);
                 const int base = qn - take;
-                int owner = lane, uq = 0;
                 const bool have = lane < take;
+                int owner = lane, uq = 0;
                 if (have) {
                     const uint32_t e = queue[base + lane];
                     owner = (int)(e >> 16);
                     uq = (int)(e & 0xffffu);
                 }
-                const float oI1 = __shfl_sync(full, I1, owner);
-                const float og1 = __shfl_sync(full, g1, owner);
                 const float oab = __shfl_sync(full, ab, owner);
                 const float ocb = __shfl_sync(full, cb, owner);
+                const float oI1 = __shfl_sync(full, I1, owner);
+                const float og1 = __shfl_sync(full, g1, owner);
+                const float oepi = __shfl_sync(full, th_epi, owner);
+                const float oapr = __shfl_sync(full, apr, owner);
+                bool won = false;
+                uint32_t eb = 0;
                 if (have) {
-                    const float yv = -(oab * (float)uq + ocb);
-                    const float rI = oI1 - bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yv, uq);
-                    const float rG = og1 - bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yv, uq);
-                    // err = rI*rI + (rG*rG)/THETA evaluated in double (THETA is a double literal), stored to float
-                    const float err = (float)((double)(rI * rI) + (double)(rG * rG) / A.THETA);
-                    if (err < 1000000.0f) {
-                        const unsigned long long key = ((unsigned long long)__float_as_uint(err) << 32) | (unsigned)uq;
-                        atomicMin(&best[owner], key);
+                    const float vf = __fadd_rn(__fmul_rn(oab, (float)uq), ocb);
+                    const int r0 = -__float2int_rz(vf);  // 0 < r0 < H by construction; == floor(-vf)
+                    const int xc = min(uq, A.W - 1);
+                    const int r1 = min(r0 + 1, A.H - 1);
+                    const unsigned of0 = (unsigned)(r0 * A.pitch_f + xc);  // planes hold < 2^31 elements (checked at upload)
+                    const float T2 = __ldg(N.theta + of0);
+                    if (orientation_gates(T2, oepi, oapr, A.lambdaL, A.lambdaTheta)) {
+                        const float yv = -vf;
+                        const float w0 = ((float)r0 + 1.0f) - yv;  // bilinear_col weights, PM.cc:46-53
+                        const float w1 = 1.0f - w0;
+                        const float i0 = (float)__ldg(N.img + (unsigned)(r0 * A.pitch_u8 + xc));
+                        const float i1 = (float)__ldg(N.img + (unsigned)(r1 * A.pitch_u8 + xc));
+                        const float gg0 = __ldg(N.grad + of0);
+                        const float gg1 = __ldg(N.grad + (unsigned)(r1 * A.pitch_f + xc));
+                        const float rI = oI1 - (i0 * w0 + i1 * w1);
+                        const float rG = og1 - (gg0 * w0 + gg1 * w1);
+                        const float ef = rI * rI + (rG * rG) * inv_theta_f;  // float shortcut of PM.cc:436
+                        if (ef < K1_ERR_LIMIT_LO) {
+                            eb = __float_as_uint(ef);
+                            const uint32_t old = atomicMin(&beste[owner], eb);
+                            const float fo = __uint_as_float(old);
+                            const float lo = fminf(ef, fo), hi = fmaxf(ef, fo);
+                            if (hi - lo <= __fmaf_rn(lo, K1_TIE_REL, 1e-30f)) atomicOr(&s_tie[wib], 1u << owner);
+                            won = eb < old;
+                        } else {  // never with u8 images (err <= ~2.1e5); keep the 1e6 limit exact anyway
+                            atomicOr(&s_tie[wib], 1u << owner);
+                        }
                     }
                 }
-                qn = base;
                 __syncwarp();
+                if (won && beste[owner] == eb) bestu[owner] = (uint32_t)uq;
+                __syncwarp();
+                qn = base;
             }
+        };
+
+        // ---------------- (B) run-by-run scan of the arc plane ----------------
+        auto push = [&](uint32_t m, int col_base) {
+            int pos = 0;
+            if (m) pos = (int)atomicAdd(&s_qn[wib], (unsigned)__popc(m));
+            while (m) {
+                const int bit = __ffs((int)m) - 1;
+                m &= m - 1;
+                queue[pos++] = ((uint32_t)lane << 16) | (uint32_t)(col_base + bit);
+            }
+            __syncwarp();
+            qn = (int)*qn_s;
+        };
+
+        const int u_end = min(u_hi, A.W - 1);
+        int u = u_lo;
+        while (__any_sync(full, u <= u_end)) {
+            uint32_t m = 0;
+            int col_base = 0;
+            if (u <= u_end) {
+                int ue = min(u | 31, u_end);
+                const int t0 = line_row_neg(ab, cb, u);
+                if (ue > u && line_row_neg(ab, cb, ue) != t0) ue = run_end(ab, cb, inv_ab, u, ue, t0);
+                if (t0 < 0 && t0 > -A.H) {  // PM.cc:408: 0 < vj < rows
+                    const uint32_t w = __ldg(arcp + (unsigned)((-t0) * A.arc_pitch + (u >> 5)));
+                    m = w & (0xffffffffu << (u & 31)) & (0xffffffffu >> (31 - (ue & 31)));
+                }
+                col_base = u & ~31;
+                u = ue + 1;
+            }
+            push(m, col_base);
+            drain(false);
+            if (lane == 0) *qn_s = (uint32_t)qn;
+            __syncwarp();
         }
+        // candidate column uj == cols reads column cols-1 (clamp-to-edge)
+        const bool extra = u_hi >= A.W && u_lo <= A.W;
+        if (__any_sync(full, extra)) {
+            uint32_t m = 0;
+            if (extra) {
+                const int t0 = line_row_neg(ab, cb, A.W);
+                if (t0 < 0 && t0 > -A.H) {
+                    const uint32_t w = __ldg(arcp + (size_t)(-t0) * A.arc_pitch + ((A.W - 1) >> 5));
+                    m = (w >> ((A.W - 1) & 31)) & 1u;
+                }
+            }
+            push(m, A.W);
+        }
+        drain(true);
         __syncwarp();
 
         // ---------------- (D) refinement + hypothesis: PM.cc:446-463, 806-829 ----------------
-        const unsigned long long key = best[lane];
-        float rho = 0.f, sig = 0.f;
-        bool found = false;
         int bj = -1;
-        if (key != ~0ull) {
-            found = true;
-            bj = (int)(unsigned)(key & 0xffffffffu);
+        if ((s_tie[wib] >> lane) & 1u) {
+            LineScan L;
+            L.ab = ab; L.cb = cb; L.I1 = I1; L.g1 = g1; L.th_epi = th_epi; L.apr = apr; L.u_lo = u_lo; L.u_hi = u_hi;
+            bj = exact_line_scan(A, N, L);
+        } else if (beste[lane] != 0x7f800000u) {
+            bj = (int)bestu[lane];
+        }
+        float rho = 0.f, sig = 0.f;
+        const bool found = bj >= 0;
+        if (found) {
             const float yb = -(ab * (float)bj + cb);
             const float rI = I1 - bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yb, bj);
             const float rG = g1 - bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yb, bj);
@@ -468,46 +709,25 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
     }
 
     // ---------------- InverseDepthHypothesisFusion, PM.cc:221-228 + 598-626 ----------------
-    if (!valid || A.probe_out || !(nh > A.lambdaN)) return;
-    int best_cnt = 0, best_a = -1;
-    for (int ia = 0; ia < nh; ++ia) {
-        int c = 0;
-        for (int ib = 0; ib < nh; ++ib) c += chi_test(hd[ia], hd[ib], hs[ia], hs[ib], A.chi_fuse) ? 1 : 0;
-        if (c > best_cnt) { best_cnt = c; best_a = ia; }
-    }
-    if (best_cnt >= A.lambdaN) {
-        // GetFusion(depthHo), PM.cc:947-970: pow(sigma,2) in double, float accumulators
-        float pjsj = 0, rsj = 0;
-        for (int ib = 0; ib < nh; ++ib) {
-            if (!chi_test(hd[best_a], hd[ib], hs[best_a], hs[ib], A.chi_fuse)) continue;
-            const double s2 = (double)hs[ib] * (double)hs[ib];
-            pjsj = (float)((double)pjsj + (double)hd[ib] / s2);
-            rsj = (float)((double)rsj + 1.0 / s2);
+    if (valid && !A.probe_out && nh > A.lambdaN) {
+        float fd, fs;
+        if (fuse_hypotheses(hd, hs, nh, A.lambdaN, A.chi_fuse, fd, fs)) {
+            A.depth[(size_t)y * A.pitch_f + x] = fd;
+            A.sigma[(size_t)y * A.pitch_f + x] = fs;
         }
-        A.depth[(size_t)y * A.pitch_f + x] = pjsj / rsj;
-        A.sigma[(size_t)y * A.pitch_f + x] = sqrtf(1 / rsj);
     }
+  }  // task loop
 }
 
-// fusion probe: one thread, same code path as the tail of k1_search
+// fusion probe: one thread, same device function as the tail of k1_search
 __global__ void k1_fusion_probe(const float* d, const float* s, int n, int lambdaN, float chi_fuse, float* out) {
-    int best_cnt = 0, best_a = -1;
-    for (int ia = 0; ia < n; ++ia) {
-        int c = 0;
-        for (int ib = 0; ib < n; ++ib) c += chi_test(d[ia], d[ib], s[ia], s[ib], chi_fuse) ? 1 : 0;
-        if (c > best_cnt) { best_cnt = c; best_a = ia; }
-    }
+    float hd[SD_MAX_NEIGHBOURS], hs[SD_MAX_NEIGHBOURS];
+    for (int i = 0; i < n; ++i) { hd[i] = d[i]; hs[i] = s[i]; }
     out[0] = out[1] = out[2] = 0.f;
-    if (best_cnt >= lambdaN) {
-        float pjsj = 0, rsj = 0;
-        for (int ib = 0; ib < n; ++ib) {
-            if (!chi_test(d[best_a], d[ib], s[best_a], s[ib], chi_fuse)) continue;
-            const double s2 = (double)s[ib] * (double)s[ib];
-            pjsj = (float)((double)pjsj + (double)d[ib] / s2);
-            rsj = (float)((double)rsj + 1.0 / s2);
-        }
-        out[0] = pjsj / rsj;
-        out[1] = sqrtf(1 / rsj);
+    float fd, fs;
+    if (fuse_hypotheses(hd, hs, n, lambdaN, chi_fuse, fd, fs)) {
+        out[0] = fd;
+        out[1] = fs;
         out[2] = 1.f;
     }
 }

@@ -25,6 +25,7 @@ print("active", len(xs), "of", W*H, "prior", plan.prior[k])
 mind, maxd = plan.prior[k]
 fx, fy, cx, cy = [np.float32(v) for v in scene.K]
 tot_c = tot_s = tot_g1 = tot_runs = tot_px = 0
+tot_q = 0.0
 for jn, j in enumerate(plan.nbrs[k]):
     F, R, t = po.pair_geometry(scene.K, plan.poses[k], scene.K, plan.poses[int(j)])
     xf = xs.astype(np.float32); yf = ys.astype(np.float32)
@@ -44,7 +45,7 @@ for jn, j in enumerate(plan.nbrs[k]):
     rot = plan.rots[k][jn]
     # sample 4000 pixels for gate statistics
     rng = np.random.default_rng(0); sel = rng.choice(len(xs), 4000, replace=False)
-    c_all = s_all = g1_all = 0
+    c_all = s_all = g1_all = q_all = 0
     for i in sel:
         if cnt[i] == 0: continue
         uj = np.arange(lo[i], hi[i]+1); vj = -np.trunc(ab[i]*uj.astype(np.float32) + cb[i]).astype(int)
@@ -56,8 +57,15 @@ for jn, j in enumerate(plan.nbrs[k]):
         d = (T - the) % 360; d = np.where(d > 180, 360-d, d); d = np.where(d > 90, 180-d, d)
         e = (T - (th1[ys[i], xs[i]] + rot)) % 360; e = np.where(e > 180, 360-e, e)
         sv = p1 & (d <= 80) & (e <= 45)
+        apr = (th1[ys[i], xs[i]] + rot) % 360
+        cen = (np.floor(apr / 11.25) + 0.5) * 11.25
+        cd = np.abs((T - cen + 180) % 360 - 180)
+        q_all += (p1 & (cd <= 45 + 5.625 + 0.05)).sum()
         c_all += len(uj); g1_all += p1.sum(); s_all += sv.sum()
-    print(f"nbr {int(j):3d} rot {rot:+.2f}: mean cand {cnt.mean():6.1f} max {cnt.max():4d}  p50/p90/p99 {np.percentile(cnt,[50,90,99])}  mean runs {runs.mean():.2f}  |ab| mean {np.abs(ab).mean():.4f} max {np.abs(ab).max():.3f}  gate1 {g1_all/max(c_all,1):.3f} surv {s_all/max(c_all,1):.4f}")
+    print(f"nbr {int(j):3d} rot {rot:+.2f}: mean cand {cnt.mean():6.1f} max {cnt.max():4d}  p50/p90/p99 {np.percentile(cnt,[50,90,99])}  mean runs {runs.mean():.2f}  |ab| mean {np.abs(ab).mean():.4f} max {np.abs(ab).max():.3f}  gate1 {g1_all/max(c_all,1):.3f} surv {s_all/max(c_all,1):.4f} queued {q_all/max(c_all,1):.4f}")
+    tot_q += q_all/max(c_all,1) * cnt.sum()
     tot_c += cnt.sum(); tot_runs += runs.sum(); tot_px += len(xs)
     tot_s += s_all / max(c_all, 1) * cnt.sum()
 print(f"total candidates/KF {tot_c/1e6:.1f} M  per pixel-nbr {tot_c/tot_px:.1f}  runs per pixel-nbr {tot_runs/tot_px:.2f}  survivors/KF ~{tot_s/1e6:.2f} M")
+
+print("queued by the arc planes /KF ~%.2f M" % (tot_q/1e6))
