@@ -142,6 +142,18 @@ float sd_rot_in_plane_median(const long long* mp1, const float* ang1, int n1, co
 int sd_pair_geometry(const float K1[4], const float Tcw1[12], const float K2[4], const float Tcw2[12], float F12[9],
                      float R21[9], float t21[3]);
 
+/* GetSearchRange, PM.cc:877-910: the column interval [umin, umax] of key frame 2 (clamped to
+ * [0, cols] inclusive, as the reference does) that the inverse-depth interval maps to for pixel (px, py). */
+int sd_search_range(const float K1[4], const float Tcw1[12], const float Tcw2[12], int cols, int px, int py, float mind,
+                    float maxd, float* umin, float* umax);
+
+/* IntraKeyFrameDepthChecking (PM.cc:486-547) / IntraKeyFrameDepthGrowing (PM.cc:549-596) on caller-owned
+ * HOST planes of w*h floats each, updated in place like the reference's cv::Mat& arguments: the
+ * planes are copied to the device, one stencil kernel runs (the same one sd_semidense launches),
+ * and the result is copied back.  Synchronous. */
+int sd_intra_depth_check_planes(sd_ctx* ctx, float* depth, float* sigma, const float* grad, int w, int h);
+int sd_intra_depth_grow_planes(sd_ctx* ctx, float* depth, float* sigma, const float* grad, int w, int h);
+
 /* ---- single-pixel probes (run the same device code as the batch kernels; for unit tests) ---- */
 /* EpipolarSearch PM.cc:385-465 for n pixels xy[2*i], xy[2*i+1] of kf1 against kf2.
  * out[4*i..] = {inverse depth, sigma, best integer uj (or -1), supported} */

@@ -907,6 +907,25 @@ void ora_search_range(const float K1[4], const float R21[9], const float t21[3],
     GetSearchRange(*umin, *umax, px, py, mind, maxd, K1[0], K1[1], K1[2], K1[3], cols, R, t);
 }
 
+/* PM.cc:486-547 / 549-596 on caller planes (w*h floats, updated in place) */
+void ora_intra_check_planes(const OraParams* p, float* depth, float* sigma, int w, int h) {
+    OraParams P;
+    if (p) P = *p; else ora_default_params(&P);
+    std::vector<float> d(depth, depth + (size_t)w * h), s(sigma, sigma + (size_t)w * h);
+    IntraKeyFrameDepthChecking(P, d, s, h, w);
+    std::memcpy(depth, d.data(), d.size() * sizeof(float));
+    std::memcpy(sigma, s.data(), s.size() * sizeof(float));
+}
+
+void ora_intra_grow_planes(const OraParams* p, float* depth, float* sigma, const float* grad, int w, int h) {
+    OraParams P;
+    if (p) P = *p; else ora_default_params(&P);
+    std::vector<float> d(depth, depth + (size_t)w * h), s(sigma, sigma + (size_t)w * h), g(grad, grad + (size_t)w * h);
+    IntraKeyFrameDepthGrowing(P, d, s, g, h, w);
+    std::memcpy(depth, d.data(), d.size() * sizeof(float));
+    std::memcpy(sigma, s.data(), s.size() * sizeof(float));
+}
+
 float ora_pixel_depth(const float K1[4], const float R21[9], const float t21[3], float uj, int px, int py) {
     M33 R;
     V3 t;

@@ -68,6 +68,8 @@ void  ora_pair_geometry(const float K1[4], const float Tcw1[12], const float K2[
                         float F12[9], float R21[9], float t21[3]);                /* PM.cc:972-987, 890-891 */
 void  ora_search_range(const float K1[4], const float R21[9], const float t21[3], int cols, int px, int py,
                        float mind, float maxd, float* umin, float* umax);         /* PM.cc:877-910 */
+void  ora_intra_check_planes(const OraParams* p, float* depth, float* sigma, int w, int h);                    /* PM.cc:486-547 */
+void  ora_intra_grow_planes(const OraParams* p, float* depth, float* sigma, const float* grad, int w, int h);  /* PM.cc:549-596 */
 float ora_pixel_depth(const float K1[4], const float R21[9], const float t21[3], float uj, int px, int py); /* PM.cc:845-875 */
 /* PM.cc:385-465 on one pixel; returns 1 if a hypothesis was produced */
 int   ora_epipolar_search(void* h, int kf1, int kf2, int x, int y, float min_depth, float max_depth, float rot,

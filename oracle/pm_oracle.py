@@ -76,6 +76,8 @@ def lib():
         L.ora_rot_in_plane_median.restype = C.c_float
         L.ora_pair_geometry.argtypes = [fp, fp, fp, fp, fp, fp, fp]
         L.ora_search_range.argtypes = [fp, fp, fp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, fp, fp]
+        L.ora_intra_check_planes.argtypes = [C.POINTER(OraParams), vp, vp, C.c_int, C.c_int]
+        L.ora_intra_grow_planes.argtypes = [C.POINTER(OraParams), vp, vp, vp, C.c_int, C.c_int]
         L.ora_pixel_depth.argtypes = [fp, fp, fp, C.c_float, C.c_int, C.c_int]
         L.ora_pixel_depth.restype = C.c_float
         L.ora_epipolar_search.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, C.c_float, fp, fp, fp, fp]
@@ -171,6 +173,28 @@ class Oracle:
         o = [C.c_float() for _ in range(4)]
         ok = self.L.ora_epipolar_search(self.h, kf1, kf2, x, y, min_depth, max_depth, rot, *[C.byref(v) for v in o])
         return ok, [v.value for v in o]
+
+
+def intra_planes(depth, sigma, grad=None, grow=False, params=None):
+    """IntraKeyFrameDepthChecking (grow=False) / IntraKeyFrameDepthGrowing (grow=True) on host planes."""
+    d = np.array(depth, np.float32, order="C")
+    s = np.array(sigma, np.float32, order="C")
+    h, w = d.shape
+    pp = C.byref(params) if params is not None else None
+    if grow:
+        g = np.ascontiguousarray(grad, np.float32)
+        lib().ora_intra_grow_planes(pp, d.ctypes.data, s.ctypes.data, g.ctypes.data, w, h)
+    else:
+        lib().ora_intra_check_planes(pp, d.ctypes.data, s.ctypes.data, w, h)
+    return d, s
+
+
+def search_range(K1, R21, t21, cols, px, py, mind, maxd):
+    a = [_f(x) for x in (K1, np.asarray(R21).reshape(-1), t21)]
+    lo, hi = C.c_float(), C.c_float()
+    lib().ora_search_range(a[0][1], a[1][1], a[2][1], int(cols), int(px), int(py), float(mind), float(maxd),
+                           C.byref(lo), C.byref(hi))
+    return lo.value, hi.value
 
 
 def stereo_search_constraints(depths):

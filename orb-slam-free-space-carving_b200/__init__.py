@@ -76,6 +76,9 @@ SYMBOLS = {
     "sd_stereo_search_constraints": (C.c_int, [_fp, C.c_int, _fp, _fp]),
     "sd_rot_in_plane_median": (C.c_float, [_vp, _fp, C.c_int, _vp, _fp, C.c_int]),
     "sd_pair_geometry": (C.c_int, [_fp, _fp, _fp, _fp, _fp, _fp, _fp]),
+    "sd_search_range": (C.c_int, [_fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, _fp, _fp]),
+    "sd_intra_depth_check_planes": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
+    "sd_intra_depth_grow_planes": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
     "sd_probe_epipolar": (C.c_int, [_vp, C.c_int, C.c_int, _ip, C.c_int, C.c_float, C.c_float, C.c_float, _fp]),
     "sd_probe_fusion": (C.c_int, [_vp, _fp, _fp, C.c_int, _fp, _fp, _ip]),
 }
@@ -138,6 +141,17 @@ def pair_geometry(K1, Tcw1, K2, Tcw2):
     if rc:
         raise SdError(rc)
     return np.array(F, np.float32).reshape(3, 3), np.array(R, np.float32).reshape(3, 3), np.array(t, np.float32)
+
+
+def search_range(K1, Tcw1, Tcw2, cols, px, py, mind, maxd):
+    """GetSearchRange (PM.cc:877-910): (umin, umax) clamped to [0, cols]."""
+    a = [_f(x) for x in (K1, np.asarray(Tcw1).reshape(-1)[:12], np.asarray(Tcw2).reshape(-1)[:12])]
+    lo, hi = C.c_float(), C.c_float()
+    rc = lib().sd_search_range(a[0][1], a[1][1], a[2][1], int(cols), int(px), int(py), float(mind), float(maxd),
+                               C.byref(lo), C.byref(hi))
+    if rc:
+        raise SdError(rc)
+    return lo.value, hi.value
 
 
 class Context:
@@ -271,6 +285,16 @@ class Context:
             self._ck(self.L.sd_timing_get(self.h, name.encode(), C.byref(ms), C.byref(n)))
             out[name] = (ms.value, n.value)
         return out
+
+    def intra_planes(self, depth, sigma, grad, grow=False):
+        """IntraKeyFrameDepthChecking / ...Growing on host planes; returns new (depth, sigma)."""
+        d = np.array(depth, np.float32, order="C")
+        s = np.array(sigma, np.float32, order="C")
+        g = np.ascontiguousarray(grad, np.float32)
+        h, w = d.shape
+        fn = self.L.sd_intra_depth_grow_planes if grow else self.L.sd_intra_depth_check_planes
+        self._ck(fn(self.h, d.ctypes.data, s.ctypes.data, g.ctypes.data, w, h))
+        return d, s
 
     def probe_epipolar(self, kf1, kf2, xy, min_depth, max_depth, rot):
         xy, xp = _i(np.asarray(xy).reshape(-1))

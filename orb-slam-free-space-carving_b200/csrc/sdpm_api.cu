@@ -730,6 +730,77 @@ int sd_pair_geometry(const float K1[4], const float Tcw1[12], const float K2[4],
     return SD_OK;
 }
 
+int sd_search_range(const float K1[4], const float Tcw1[12], const float Tcw2[12], int cols, int px, int py, float mind, float maxd,
+                    float* umin_out, float* umax_out) {
+    if (!K1 || !Tcw1 || !Tcw2 || !umin_out || !umax_out || cols < 1) return SD_ERR_INVALID_ARG;
+    // PM.cc:877-910, same operation order as stage (A) of k1_search
+    float R1[9], t1[3], R2[9], t2[3], R21[9], t21[3];
+    for (int r = 0; r < 3; ++r) {
+        for (int col = 0; col < 3; ++col) { R1[r * 3 + col] = Tcw1[r * 4 + col]; R2[r * 3 + col] = Tcw2[r * 4 + col]; }
+        t1[r] = Tcw1[r * 4 + 3];
+        t2[r] = Tcw2[r * 4 + 3];
+    }
+    geom::relative_pose(R1, t1, R2, t2, R21, t21);
+    const float fx = K1[0], fy = K1[1], cx = K1[2], cy = K1[3];
+    const float xp0 = ((float)px - cx) / fx, xp1 = ((float)py - cy) / fy;
+    const float q0 = R21[0] * xp0 + R21[1] * xp1 + R21[2] * 1.0f;
+    const float q2 = R21[6] * xp0 + R21[7] * xp1 + R21[8] * 1.0f;
+    const float xmin0 = (float)((double)q0 * (double)mind + (double)t21[0]);
+    const float xmin2 = (float)((double)q2 * (double)mind + (double)t21[2]);
+    const float xmax0 = (float)((double)q0 * (double)maxd + (double)t21[0]);
+    const float xmax2 = (float)((double)q2 * (double)maxd + (double)t21[2]);
+    float umin = fx * xmin0 / xmin2 + cx;
+    float umax = fx * xmax0 / xmax2 + cx;
+    if (umin > umax) { float t = umax; umax = umin; umin = t; }
+    const float colsf = (float)cols;
+    if (umin < 0) umin = 0;
+    if (umax < 0) umax = 0;
+    if (umin > colsf) umin = colsf;
+    if (umax > colsf) umax = colsf;
+    *umin_out = umin;
+    *umax_out = umax;
+    return SD_OK;
+}
+
+static int intra_planes(sd_ctx* c, float* depth, float* sigma, const float* grad, int w, int h, bool grow) {
+    if (!c || !depth || !sigma || !grad || w < 8 || h < 8 || (long long)(w + 128) * h >= (1ll << 30))
+        return fail(c, SD_ERR_INVALID_ARG, "sd_intra_depth_*_planes: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    const size_t bytes = (size_t)w * h * sizeof(float);
+    float* d = nullptr;
+    CU(c, cudaMalloc(&d, 5 * bytes));
+    float *d_depth = d, *d_sigma = d + (size_t)w * h, *d_grad = d + 2 * (size_t)w * h, *o_depth = d + 3 * (size_t)w * h,
+          *o_sigma = d + 4 * (size_t)w * h;
+    cudaError_t e = cudaMemcpyAsync(d_depth, depth, bytes, cudaMemcpyHostToDevice, c->s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_sigma, sigma, bytes, cudaMemcpyHostToDevice, c->s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_grad, grad, bytes, cudaMemcpyHostToDevice, c->s_main);
+    if (e == cudaSuccess) {
+        StencilArgs S;
+        S.W = w; S.H = h; S.pitch_f = w; S.border = c->P.border;
+        S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f; S.grad = d_grad;
+        S.depth_in = d_depth; S.sigma_in = d_sigma; S.depth_out = o_depth; S.sigma_out = o_sigma;
+        dim3 blk(32, 8), grd((w + 31) / 32, (h + 7) / 8);
+        if (grow) k3_intra_grow<<<grd, blk, 0, c->s_main>>>(S);
+        else k2_intra_check<<<grd, blk, 0, c->s_main>>>(S);
+        c->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(depth, o_depth, bytes, cudaMemcpyDeviceToHost, c->s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sigma, o_sigma, bytes, cudaMemcpyDeviceToHost, c->s_main);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->s_main);
+    cudaFree(d);
+    if (e != cudaSuccess) return fail(c, SD_ERR_CUDA, "sd_intra_depth_*_planes: %s", cudaGetErrorString(e));
+    return SD_OK;
+}
+
+int sd_intra_depth_check_planes(sd_ctx* c, float* depth, float* sigma, const float* grad, int w, int h) {
+    return intra_planes(c, depth, sigma, grad, w, h, false);
+}
+
+int sd_intra_depth_grow_planes(sd_ctx* c, float* depth, float* sigma, const float* grad, int w, int h) {
+    return intra_planes(c, depth, sigma, grad, w, h, true);
+}
+
 // ---- probes ----
 
 int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float min_invdepth, float max_invdepth, float rot_deg, float* out) {

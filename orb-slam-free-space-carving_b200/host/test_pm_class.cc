@@ -1,0 +1,142 @@
+// Test driver of the C++ host mirror (ProbabilityMapping.h): reads a scene file written by
+// tests/test_host_class.py, runs ProbabilityMapping::Run() through the class surface and writes the
+// KeyFrameView results back for the Python side to compare with the oracle.
+//
+//   test_pm_class <scene.bin> <out.bin> [obj path]   full run on cuda:0
+//   test_pm_class --no-device-check                  exits 0 iff construction fails loudly without a GPU
+//
+// scene.bin (little endian): int32 nkf, w, h, covis_n; then per key frame:
+//   int32 id; float K[4]; float Tcw[12]; int32 ncov; int32 cov[ncov] (indices into the file order);
+//   int32 nd; float depths[nd]; int32 nkp; int64 mp[nkp]; float ang[nkp]; uint8 image[w*h]
+// then int32 nprobe; per probe: int32 kf1_index, kf2_index, x, y; float min_depth, max_depth, rot
+// out.bin: per key frame: int32 semidense_flag, interKF_flag; float depth[w*h], sigma[w*h]; int32 has_points;
+//   float points[3*w*h] if has_points; then per probe: float depth, sigma, best_u, best_v, supported, umin, umax
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <stdexcept>
+#include <vector>
+
+#include "ProbabilityMapping.h"
+
+using namespace sdpm_host;
+
+namespace {
+template <typename T>
+void rd(std::FILE* f, T* p, size_t n) {
+    if (n && std::fread(p, sizeof(T), n, f) != n) throw std::runtime_error("scene file truncated");
+}
+template <typename T>
+void wr(std::FILE* f, const T* p, size_t n) {
+    if (n && std::fwrite(p, sizeof(T), n, f) != n) throw std::runtime_error("short write");
+}
+struct Probe {
+    int kf1, kf2, x, y;
+    float mind, maxd, rot;
+};
+}  // namespace
+
+int main(int argc, char** argv) {
+    if (argc >= 2 && !std::strcmp(argv[1], "--no-device-check")) {
+        Map map;
+        try {
+            ProbabilityMapping pm(&map, 0);
+        } catch (const std::exception& e) {
+            std::printf("construction failed loudly: %s\n", e.what());
+            return 0;
+        }
+        std::printf("a CUDA device is present: construction succeeded\n");
+        return 0;
+    }
+    if (argc < 3) {
+        std::fprintf(stderr, "usage: %s scene.bin out.bin [cloud.obj]\n", argv[0]);
+        return 2;
+    }
+    try {
+        std::FILE* f = std::fopen(argv[1], "rb");
+        if (!f) throw std::runtime_error("cannot open scene file");
+        int32_t hdr[4];
+        rd(f, hdr, 4);
+        const int nkf = hdr[0], w = hdr[1], h = hdr[2], covis_n = hdr[3];
+        std::vector<std::unique_ptr<KeyFrameView>> kfs;
+        std::vector<std::vector<uint8_t>> images(nkf);
+        std::vector<std::vector<int32_t>> cov(nkf);
+        for (int i = 0; i < nkf; ++i) {
+            std::unique_ptr<KeyFrameView> kf(new KeyFrameView());
+            int32_t id, n;
+            rd(f, &id, 1);
+            kf->mnId = id;
+            rd(f, kf->K, 4);
+            rd(f, kf->Tcw, 12);
+            rd(f, &n, 1);
+            cov[i].resize(n);
+            rd(f, cov[i].data(), n);
+            rd(f, &n, 1);
+            kf->point_depths.resize(n);
+            rd(f, kf->point_depths.data(), n);
+            rd(f, &n, 1);
+            kf->map_points.resize(n);
+            kf->keypoint_angles.resize(n);
+            rd(f, kf->map_points.data(), n);
+            rd(f, kf->keypoint_angles.data(), n);
+            images[i].resize((size_t)w * h);
+            rd(f, images[i].data(), images[i].size());
+            kf->im_ = PlaneView<const uint8_t>(images[i].data(), h, w);
+            kfs.push_back(std::move(kf));
+        }
+        int32_t nprobe = 0;
+        rd(f, &nprobe, 1);
+        std::vector<Probe> probes(nprobe);
+        for (auto& p : probes) {
+            int32_t v[4];
+            rd(f, v, 4);
+            p.kf1 = v[0]; p.kf2 = v[1]; p.x = v[2]; p.y = v[3];
+            float g[3];
+            rd(f, g, 3);
+            p.mind = g[0]; p.maxd = g[1]; p.rot = g[2];
+        }
+        std::fclose(f);
+
+        Map map;
+        for (int i = 0; i < nkf; ++i) {
+            for (int c : cov[i]) kfs[i]->covisible.push_back(kfs[c].get());
+            map.keyframes.push_back(kfs[i].get());
+        }
+
+        ProbabilityMapping pm(&map, 0, covis_n);
+        pm.Run();
+
+        std::FILE* o = std::fopen(argv[2], "wb");
+        if (!o) throw std::runtime_error("cannot open output file");
+        for (int i = 0; i < nkf; ++i) {
+            KeyFrameView* kf = kfs[i].get();
+            int32_t flags[2] = {kf->semidense_flag_, kf->interKF_depth_flag_};
+            wr(o, flags, 2);
+            std::vector<float> zero((size_t)w * h, 0.f);
+            wr(o, kf->depth_map_.size() ? kf->depth_map_.data() : zero.data(), (size_t)w * h);
+            wr(o, kf->depth_sigma_.size() ? kf->depth_sigma_.data() : zero.data(), (size_t)w * h);
+            int32_t hp = kf->SemiDensePointSets_.size() == (size_t)3 * w * h;
+            wr(o, &hp, 1);
+            if (hp) wr(o, kf->SemiDensePointSets_.data(), (size_t)3 * w * h);
+        }
+        for (const auto& p : probes) {
+            ProbabilityMapping::depthHo dh;
+            float bu = 0, bv = 0, F12[9];
+            KeyFrameView *a = kfs[p.kf1].get(), *b = kfs[p.kf2].get();
+            pm.ComputeFundamental(a, b, F12);
+            pm.EpipolarSearch(a, b, p.x, p.y, (float)a->im_.at(p.y, p.x), p.mind, p.maxd, &dh, F12, bu, bv, 0.f, p.rot);
+            float umin = 0, umax = 0;
+            pm.GetSearchRange(umin, umax, p.x, p.y, p.mind, p.maxd, a, b);
+            float rec[7] = {dh.depth, dh.sigma, bu, bv, dh.supported ? 1.f : 0.f, umin, umax};
+            wr(o, rec, 7);
+        }
+        std::fclose(o);
+        if (argc >= 4 && !pm.SavePointCloudObj(argv[3])) return 1;
+        std::printf("ok: %d key frames %dx%d, covisN %d, %d probes\n", nkf, w, h, covis_n, (int)nprobe);
+        return 0;
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "test_pm_class: %s\n", e.what());
+        return 1;
+    }
+}
