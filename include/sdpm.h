@@ -128,7 +128,7 @@ int sd_span_begin(sd_ctx* ctx);
 int sd_span_end(sd_ctx* ctx, double* ms);
 /* Per-kernel device timing (CUDA events on the launching stream). enable=1 starts collecting. */
 int sd_timing_enable(sd_ctx* ctx, int enable);
-/* names: "grad", "search", "intra", "grow", "inter", "points"; returns accumulated ms and launches */
+/* names: "grad", "search", "intra" (checking + growing, one kernel), "inter", "points"; returns accumulated ms and launches */
 int sd_timing_get(sd_ctx* ctx, const char* name, double* ms, uint64_t* launches);
 int sd_timing_reset(sd_ctx* ctx);
 

@@ -280,7 +280,7 @@ class Context:
 
     def timing(self):
         out = {}
-        for name in ("grad", "search", "intra", "grow", "inter", "points"):
+        for name in ("grad", "search", "intra", "inter", "points"):
             ms, n = C.c_double(), C.c_uint64()
             self._ck(self.L.sd_timing_get(self.h, name.encode(), C.byref(ms), C.byref(n)))
             out[name] = (ms.value, n.value)

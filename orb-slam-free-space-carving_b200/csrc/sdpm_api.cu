@@ -20,8 +20,8 @@ using namespace sdpm;
 
 namespace {
 
-enum { T_GRAD = 0, T_SEARCH, T_INTRA, T_GROW, T_INTER, T_POINTS, T_COUNT };
-const char* kTimerNames[T_COUNT] = {"grad", "search", "intra", "grow", "inter", "points"};
+enum { T_GRAD = 0, T_SEARCH, T_INTRA, T_INTER, T_POINTS, T_COUNT };
+const char* kTimerNames[T_COUNT] = {"grad", "search", "intra", "inter", "points"};
 
 struct Slot {
     int id = -1;
@@ -32,8 +32,10 @@ struct Slot {
     float *grad = nullptr, *theta = nullptr, *depth = nullptr, *sigma = nullptr, *depth_chk = nullptr;
     uint32_t* arc = nullptr;  // SD_ARC_PLANES orientation-arc bit planes (k0_gradient)
     float* points = nullptr;
-    uint32_t* list = nullptr;
+    uint32_t* list = nullptr;   // active pixels (k0_gradient), input of k1_search
+    uint32_t* vlist = nullptr;  // pixels carrying a depth after the intra-KF stage (k23_intra), input of k4_inter_check
     KfMeta* meta = nullptr;
+    bool vlist_ok = false;      // vlist / meta->valid_count describe `depth`
     bool has_semidense = false, has_checked = false, has_points = false, pose_changed = false;
     cudaEvent_t ev_up = nullptr;  // upload + K0 done (s_up)
     cudaEvent_t ev_dn = nullptr;  // last download issued (s_dn)
@@ -103,7 +105,7 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     const size_t uplane = align_up((size_t)c->pitch_u8 * c->H, 256);
     const size_t lplane = align_up((size_t)c->W * c->H * sizeof(uint32_t), 256);
     const size_t aplane = align_up((size_t)SD_ARC_PLANES * c->H * c->arc_pitch * sizeof(uint32_t), 256);
-    const size_t total = uplane + 5 * fplane + aplane + lplane + 256;
+    const size_t total = uplane + 5 * fplane + aplane + 2 * lplane + 256;
     cudaError_t e = cudaMalloc(&s->slab, total);
     if (e != cudaSuccess) {
         delete s;
@@ -118,6 +120,7 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->sigma = (float*)p; p += fplane;
     s->depth_chk = (float*)p; p += fplane;
     s->list = (uint32_t*)p; p += lplane;
+    s->vlist = (uint32_t*)p; p += lplane;
     s->meta = (KfMeta*)p;
     cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_dn, cudaEventDisableTiming);
@@ -218,7 +221,7 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         s->id = kf_id;
         c->kfs[kf_id] = s;
     }
-    s->has_semidense = s->has_checked = s->has_points = s->pose_changed = false;
+    s->has_semidense = s->has_checked = s->has_points = s->pose_changed = s->vlist_ok = false;
     s->dn_pending = false;
     std::memcpy(s->K, K, sizeof(s->K));
     set_pose_fields(s, Tcw);
@@ -310,6 +313,12 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
             delete c;
             return SD_ERR_CUDA;
         }
+        if (cudaFuncSetAttribute(k23_intra<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K23_SMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(k23_intra<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K23_SMEM) != cudaSuccess ||
+            cudaFuncSetAttribute(k23_intra<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)K23_SMEM) != cudaSuccess) {
+            delete c;
+            return SD_ERR_CUDA;
+        }
         c->sm_count = prop.multiProcessorCount;
         c->k1_grid = c->sm_count * per_sm;
     }
@@ -387,30 +396,32 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
     }
+    // k1_search scatters its results into the context's scratch planes (zero = no depth); k23_intra
+    // reads them with a halo and writes the key frame's own planes
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
-    CU(c, cudaMemsetAsync(s->depth, 0, fplane, c->s_main));
-    CU(c, cudaMemsetAsync(s->sigma, 0, fplane, c->s_main));
-    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), c->s_main));
+    CU(c, cudaMemsetAsync(c->tmp_depth, 0, fplane, c->s_main));
+    CU(c, cudaMemsetAsync(c->tmp_sigma, 0, fplane, c->s_main));
+    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int) + sizeof(int), c->s_main));  // + valid_count
+    A.depth = c->tmp_depth;
+    A.sigma = c->tmp_sigma;
     {
         ScopedTimer t(c, c->s_main, T_SEARCH);
         k1_search<<<c->k1_grid, K1_WARPS * 32, 0, c->s_main>>>(A);
     }
-    StencilArgs S;
-    S.W = c->W; S.H = c->H; S.pitch_f = c->pitch_f; S.border = c->P.border;
-    S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f; S.grad = s->grad;
-    dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
     {
         ScopedTimer t(c, c->s_main, T_INTRA);
-        S.depth_in = s->depth; S.sigma_in = s->sigma; S.depth_out = c->tmp_depth; S.sigma_out = c->tmp_sigma;
-        k2_intra_check<<<grd, blk, 0, c->s_main>>>(S);
-    }
-    {
-        ScopedTimer t(c, c->s_main, T_GROW);
-        S.depth_in = c->tmp_depth; S.sigma_in = c->tmp_sigma; S.depth_out = s->depth; S.sigma_out = s->sigma;
-        k3_intra_grow<<<grd, blk, 0, c->s_main>>>(S);
+        IntraArgs S;
+        S.W = c->W; S.H = c->H; S.pitch_in = c->pitch_f; S.pitch_out = c->pitch_f; S.border = c->P.border; S.vec_ok = 1;
+        S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f;
+        S.depth_in = c->tmp_depth; S.sigma_in = c->tmp_sigma; S.grad = s->grad;
+        S.depth_out = s->depth; S.sigma_out = s->sigma; S.depth_copy = s->depth_chk;
+        S.vlist = s->vlist; S.vcount = &s->meta->valid_count;
+        dim3 grd((c->W + K23_TW - 1) / K23_TW, (c->H + K23_TH - 1) / K23_TH);
+        k23_intra<true, true><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
     }
     CU(c, cudaGetLastError());
     s->has_semidense = true;
+    s->vlist_ok = true;
     s->has_checked = false;
     s->has_points = false;
     return SD_OK;
@@ -428,12 +439,15 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
     A.chi_inter = c->chi_inter_f;
     A.depth_in = s->depth;
     A.depth_out = s->depth_chk;
+    A.vlist = s->vlist;
+    A.vcount = &s->meta->valid_count;
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
         if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
         if (!nb->has_semidense) return fail(c, SD_ERR_NOT_READY, "neighbour key frame %d has no semi-dense maps", nbr_ids[j]);
         InterNbr& N = A.nb[j];
         geom::relative_pose(s->Rcw, s->tcw, nb->Rcw, nb->tcw, N.R, N.t);
+        for (int k = 0; k < 3; ++k) { N.Rd2[k] = (double)N.R[6 + k]; N.td[k] = (double)N.t[k]; }
         N.fx = nb->K[0]; N.fy = nb->K[1]; N.cx = nb->K[2]; N.cy = nb->K[3];
         N.depth = nb->depth;
         N.sigma = nb->sigma;
@@ -442,10 +456,22 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
     }
+    if (!s->vlist_ok) {  // maps installed by sd_import_maps: rebuild the list and the plane k4 patches
+        const size_t pb = (size_t)c->pitch_f * sizeof(float);
+        CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_main));
+        CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_main));
+        dim3 grd((c->W + 31) / 32, (c->H + 7) / 8);
+        k_build_vlist<<<grd, 256, 0, c->s_main>>>(s->depth, c->pitch_f, c->W, c->H, s->vlist, &s->meta->valid_count);
+        c->launches++;
+        s->vlist_ok = true;
+    } else if (s->has_checked) {  // a repeated check starts again from the intra-KF map
+        const size_t pb = (size_t)c->pitch_f * sizeof(float);
+        CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_main));
+    }
     {
         ScopedTimer t(c, c->s_main, T_INTER);
-        dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
-        k4_inter_check<<<grd, blk, 0, c->s_main>>>(A);
+        const int worst = (c->W - 4) * (c->H - 4);  // the list holds pixels inside the 2-px frame only
+        k4_inter_check<<<(worst + 127) / 128, 128, 0, c->s_main>>>(A);
     }
     CU(c, cudaGetLastError());
     s->has_checked = true;
@@ -577,6 +603,7 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     CU(c, cudaMemcpy2DAsync(s->sigma, pb, sigma_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     s->has_semidense = true;
     s->has_checked = false;
+    s->vlist_ok = false;
     return SD_OK;
 }
 
@@ -775,13 +802,15 @@ static int intra_planes(sd_ctx* c, float* depth, float* sigma, const float* grad
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_sigma, sigma, bytes, cudaMemcpyHostToDevice, c->s_main);
     if (e == cudaSuccess) e = cudaMemcpyAsync(d_grad, grad, bytes, cudaMemcpyHostToDevice, c->s_main);
     if (e == cudaSuccess) {
-        StencilArgs S;
-        S.W = w; S.H = h; S.pitch_f = w; S.border = c->P.border;
+        IntraArgs S;
+        S.W = w; S.H = h; S.pitch_in = w; S.pitch_out = w; S.border = c->P.border;
+        S.vec_ok = (w % 4 == 0) && (((size_t)w * h) % 4 == 0);  // the five planes are carved out of one allocation
         S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f; S.grad = d_grad;
         S.depth_in = d_depth; S.sigma_in = d_sigma; S.depth_out = o_depth; S.sigma_out = o_sigma;
-        dim3 blk(32, 8), grd((w + 31) / 32, (h + 7) / 8);
-        if (grow) k3_intra_grow<<<grd, blk, 0, c->s_main>>>(S);
-        else k2_intra_check<<<grd, blk, 0, c->s_main>>>(S);
+        S.depth_copy = nullptr; S.vlist = nullptr; S.vcount = nullptr;
+        dim3 grd((w + K23_TW - 1) / K23_TW, (h + K23_TH - 1) / K23_TH);
+        if (grow) k23_intra<false, true><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
+        else k23_intra<true, false><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
         c->launches++;
         e = cudaGetLastError();
     }

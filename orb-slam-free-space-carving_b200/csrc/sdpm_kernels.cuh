@@ -2,8 +2,8 @@
 //
 //   K0 k0_gradient     image -> GradImg / GradTheta / orientation-arc bit planes / active-pixel list / I_stddev sums
 //   K1 k1_search       per active pixel: EpipolarSearch in N neighbours + InverseDepthHypothesisFusion
-//   K2 k2_intra_check  IntraKeyFrameDepthChecking           (3x3 chi-square stencil)
-//   K3 k3_intra_grow   IntraKeyFrameDepthGrowing            (3x3 chi-square stencil)
+//   K2+K3 k23_intra    IntraKeyFrameDepthChecking + IntraKeyFrameDepthGrowing (3x3 chi-square stencils,
+//                      one pass) + the valid-pixel list K4 consumes
 //   K4 k4_inter_check  InterKeyFrameDepthChecking           (projection into N neighbours + Gauss-Newton)
 //   K5 k5_pointset     UpdateSemiDensePointSet              (back-projection to world)
 //
@@ -31,7 +31,7 @@ struct KfMeta {  // device-resident per key frame
     float istddev;             // KeyFrame::I_stddev
     int active_count;          // entries in the active-pixel list
     unsigned int k1_task;      // next 32-entry task of the running k1_search launch (zeroed before each launch)
-    unsigned int pad_;
+    int valid_count;           // entries in the valid-pixel list written by k23_intra (zeroed before each launch)
 };
 
 struct NbrConst {  // per neighbour, warp-uniform, lives in kernel parameter (constant) space
@@ -68,19 +68,25 @@ struct SearchArgs {
     NbrConst nb[SD_MAX_NEIGHBOURS];
 };
 
-struct StencilArgs {
-    int W, H, pitch_f, border;
+struct IntraArgs {  // k23_intra: IntraKeyFrameDepthChecking + IntraKeyFrameDepthGrowing in one pass
+    int W, H, pitch_in, pitch_out, border;
+    int vec_ok;  // 1: pitch_out % 4 == 0 and every output base pointer is 16-byte aligned (float4 stores)
     float lambdaG, chi_fuse;
-    const float* depth_in;
+    const float* depth_in;   // K1 output (or caller planes)
     const float* sigma_in;
-    const float* grad;
+    const float* grad;       // read only by the growing stage, only where it can act
     float* depth_out;
     float* sigma_out;
+    float* depth_copy;       // nullable: second copy of depth_out (the plane k4_inter_check patches)
+    uint32_t* vlist;         // nullable: compacted (y << 16 | x) of pixels with depth_out > 1e-6 inside the 2-px frame
+    int* vcount;             // nullable: entries in vlist (zeroed before the launch)
 };
 
 struct InterNbr {
-    float R[9];  // Rji, PM.cc:643
-    float t[3];  // tji, PM.cc:644
+    float R[9];    // Rji, PM.cc:643
+    float t[3];    // tji, PM.cc:644
+    double Rd2[3]; // Rji row 2 as doubles (operands of the double-accumulated dot product, PM.cc:684-686)
+    double td[3];  // tji as doubles (gemm beta*C epilogue, PM.cc:678)
     float fx, fy, cx, cy;  // K of neighbour j, PM.cc:675
     const float* depth;
     const float* sigma;
@@ -91,7 +97,9 @@ struct InterArgs {
     float fx, fy, cx, cy;
     float chi_inter;  // smallest float >= 3.84
     const float* depth_in;
-    float* depth_out;
+    float* depth_out;          // pre-filled with a copy of depth_in (k23_intra's depth_copy); patched at the listed pixels
+    const uint32_t* vlist;     // pixels to check: depth_in > 1e-6, inside the 2-px frame (PM.cc:659-662)
+    const int* vcount;
     InterNbr nb[SD_MAX_NEIGHBOURS];
 };
 
@@ -396,8 +404,10 @@ __device__ __forceinline__ bool chi_test_q(float a, float b, float qa, float qb,
     const float dl = a - b;
     const float num = dl * dl;
     const float approx = num * ra + num * rb;
-    if (approx < thr_lo) return true;
-    if (approx > thr_hi) return false;
+    if (fminf(qa, qb) > 1e-30f) {  // reciprocals of tinier squares overflow: the estimate would not track the quotient
+        if (approx < thr_lo) return true;
+        if (approx > thr_hi) return false;
+    }
     return num / qa + num / qb < thr;
 }
 
@@ -733,163 +743,310 @@ __global__ void k1_fusion_probe(const float* d, const float* s, int n, int lambd
 }
 
 // ------------------------------------------------------------------------------------------------
-// K2: IntraKeyFrameDepthChecking, PM.cc:486-547.  out = in, except valid interior pixels.
+// K2+K3: IntraKeyFrameDepthChecking (PM.cc:486-547) followed by IntraKeyFrameDepthGrowing
+// (PM.cc:549-596), one pass.  A 64x16 output tile per block; the inputs are staged in shared memory
+// with a 2-pixel halo, the checking stage is evaluated on the tile + 1-pixel halo (the growing stage
+// of a tile pixel reads the CHECKED maps of its 8 neighbours), the growing stage on the tile.
+//
+// Only ~1/4 of the pixels carry a depth, so the block first compacts the valid pixels of its input
+// region into a shared-memory list and runs the checking stage over the list (dense lanes).  The
+// GetFusion terms of a hypothesis (PM.cc:956-958: d/pow(sigma,2) and 1/pow(sigma,2), in double) do not
+// depend on which centre pixel asks for them, so they are computed once per valid pixel instead of
+// once per (centre, neighbour) pair.
+//
+// The growing stage acts on pixels WITHOUT a depth.  ChiTest(neighbour, centre) divides by the
+// centre's sigma^2; with sigma == 0 (what every invalid pixel has inside the pipeline: K1 never
+// writes it and the checking stage zeroes what it rejects) the statistic is +inf or NaN and nothing
+// is compatible, so those pixels are skipped without touching `grad`.  Any other
+// sigma takes the general path, which is the reference's loop verbatim.
+// Template flags select the stages (the two-stage pipeline, or one stage alone for the
+// caller-plane entry points sd_intra_depth_check_planes / sd_intra_depth_grow_planes).
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k2_intra_check(const StencilArgs A) {
-    const int px = blockIdx.x * blockDim.x + threadIdx.x;
-    const int py = blockIdx.y * blockDim.y + threadIdx.y;
-    if (px >= A.W || py >= A.H) return;
-    const size_t o = (size_t)py * A.pitch_f + px;
-    const float dc = A.depth_in[o], sc = A.sigma_in[o];
-    float dn = dc, sn = sc;
-    if (px >= A.border && px < A.W - A.border && py >= A.border && py < A.H - A.border && dc > SD_EPS_F) {
-        // compatible neighbours in raster order, then the pixel itself (PM.cc:504-522), fused by GetFusion
-        float pjsj = 0, rsj = 0, min_sigma = 0;
-        int ncomp = 0;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) {
-            const int dy = k / 3 - 1, dx = k % 3 - 1;
-            if (dy == 0 && dx == 0) continue;
-            const size_t q = (size_t)(py + dy) * A.pitch_f + (px + dx);
-            const float d = A.depth_in[q];
-            if (d > SD_EPS_F) {
-                const float s = A.sigma_in[q];
-                if (chi_test(d, dc, s, sc, A.chi_fuse)) {
-                    const double s2 = (double)s * (double)s;
-                    pjsj = (float)((double)pjsj + (double)d / s2);
-                    rsj = (float)((double)rsj + 1.0 / s2);
-                    // temp_min_sigma starts at compatible_ho[0].sigma; pow(s,2) < pow(min,2) in double
-                    if (ncomp == 0 || s2 < (double)min_sigma * (double)min_sigma) min_sigma = s;
-                    ++ncomp;
-                }
+constexpr int K23_TW = 64, K23_TH = 16, K23_THREADS = 256;
+constexpr int K23_IW = K23_TW + 4, K23_IH = K23_TH + 4;
+constexpr int K23_NPIX = K23_IW * K23_IH;  // 1360
+constexpr size_t K23_SMEM = (size_t)K23_NPIX * (2 * sizeof(double) + 5 * sizeof(float) + sizeof(unsigned short));
+
+template <bool CHECK, bool GROW>
+__global__ void __launch_bounds__(K23_THREADS) k23_intra(const IntraArgs A) {
+    extern __shared__ __align__(16) unsigned char k23_smem[];
+    double* s_r = reinterpret_cast<double*>(k23_smem);  // 1 / sigma^2 (double)
+    double* s_dq = s_r + K23_NPIX;                      // d / sigma^2 (double)
+    float* s_d = reinterpret_cast<float*>(s_dq + K23_NPIX);
+    float* s_s = s_d + K23_NPIX;
+    float* s_d2 = s_s + K23_NPIX;  // after the checking stage
+    float* s_s2 = s_d2 + K23_NPIX;
+    float* s_rq = s_s2 + K23_NPIX;  // 1 / (sigma*sigma) in float: only steers the division-free chi test
+    unsigned short* s_list = reinterpret_cast<unsigned short*>(s_rq + K23_NPIX);
+    __shared__ int s_n, s_vbase;
+    __shared__ int s_wcnt[K23_THREADS / 32];
+
+    const unsigned full = 0xffffffffu;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int x0 = blockIdx.x * K23_TW - 2, y0 = blockIdx.y * K23_TH - 2;
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+
+    // ---- stage inputs (halo 2), compact the valid pixels of the region ----
+    for (int i0 = 0; i0 < K23_NPIX; i0 += K23_THREADS) {
+        const int i = i0 + tid;
+        bool valid = false;
+        if (i < K23_NPIX) {
+            const int r = i / K23_IW, c = i - r * K23_IW;
+            const int y = y0 + r, x = x0 + c;
+            float d = 0.f, s = 0.f;
+            if (x >= 0 && x < A.W && y >= 0 && y < A.H) {
+                const size_t o = (size_t)y * A.pitch_in + x;
+                d = __ldg(A.depth_in + o);
+                s = __ldg(A.sigma_in + o);
+                valid = d > SD_EPS_F;
             }
+            s_d[i] = d; s_s[i] = s; s_d2[i] = d; s_s2[i] = s;
         }
-        {
-            const double s2 = (double)sc * (double)sc;
-            pjsj = (float)((double)pjsj + (double)dc / s2);
-            rsj = (float)((double)rsj + 1.0 / s2);
-            if (ncomp == 0 || s2 < (double)min_sigma * (double)min_sigma) min_sigma = sc;
-            ++ncomp;
-        }
-        if (ncomp >= 3) {
-            dn = pjsj / rsj;
-            sn = min_sigma;  // PM.cc:531: min sigma, not the fused sigma
-        } else {
-            dn = 0.0f;
-            sn = 0.0f;
+        if (CHECK) {
+            const unsigned bal = __ballot_sync(full, valid);
+            int base = 0;
+            if (lane == 0 && bal) base = atomicAdd(&s_n, __popc(bal));
+            base = __shfl_sync(full, base, 0);
+            if (valid) s_list[base + __popc(bal & ((1u << lane) - 1u))] = (unsigned short)i;
         }
     }
-    A.depth_out[o] = dn;
-    A.sigma_out[o] = sn;
-}
+    __syncthreads();
 
-// ------------------------------------------------------------------------------------------------
-// K3: IntraKeyFrameDepthGrowing, PM.cc:549-596.  (A no-op in practice: the centre sigma is 0)
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k3_intra_grow(const StencilArgs A) {
-    const int px = blockIdx.x * blockDim.x + threadIdx.x;
-    const int py = blockIdx.y * blockDim.y + threadIdx.y;
-    if (px >= A.W || py >= A.H) return;
-    const size_t o = (size_t)py * A.pitch_f + px;
-    const float dc = A.depth_in[o], sc = A.sigma_in[o];
-    float dn = dc, sn = sc;
-    if (px >= A.border && px < A.W - A.border && py >= A.border && py < A.H - A.border && dc <= SD_EPS_F &&
-        !(A.grad[o] < A.lambdaG)) {
-        float pjsj = 0, rsj = 0, min_sigma = 0;
-        int nsup = 0;
-#pragma unroll
-        for (int k = 0; k < 9; ++k) {
-            const int dy = k / 3 - 1, dx = k % 3 - 1;
-            if (dy == 0 && dx == 0) continue;
-            const size_t q = (size_t)(py + dy) * A.pitch_f + (px + dx);
-            const float d = A.depth_in[q], s = A.sigma_in[q];
-            if (chi_test(d, dc, s, sc, A.chi_fuse)) {
-                // GetFusion(pairs), PM.cc:926-945
-                const double s2 = (double)s * (double)s;
-                pjsj = (float)((double)pjsj + (double)d / s2);
-                rsj = (float)((double)rsj + 1.0 / s2);
-                if (nsup == 0 || s < min_sigma) min_sigma = s;
-                ++nsup;
-            }
+    if (CHECK) {
+        const int n = s_n;
+        // ---- per valid pixel: the GetFusion terms (PM.cc:956-958) and the float reciprocal ----
+        for (int k = tid; k < n; k += K23_THREADS) {
+            const int i = s_list[k];
+            const float d = s_d[i], s = s_s[i];
+            const double sq = (double)s * (double)s;  // pow(sigma, 2)
+            s_r[i] = 1.0 / sq;
+            s_dq[i] = (double)d / sq;
+            s_rq[i] = 1.0f / (s * s);
         }
-        if (nsup >= 2) {
-            dn = pjsj / rsj;
-            sn = min_sigma;
-        }
-    }
-    A.depth_out[o] = dn;
-    A.sigma_out[o] = sn;
-}
-
-// ------------------------------------------------------------------------------------------------
-// K4: InterKeyFrameDepthChecking, PM.cc:628-799, snapshot semantics.
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k4_inter_check(const __grid_constant__ InterArgs A) {
-    const int px = blockIdx.x * blockDim.x + threadIdx.x;
-    const int py = blockIdx.y * blockDim.y + threadIdx.y;
-    if (px >= A.W || py >= A.H) return;
-    const size_t o = (size_t)py * A.pitch_f + px;
-    const float depthp = A.depth_in[o];
-    float out = depthp;
-    if (px >= 2 && px < A.W - 2 && py >= 2 && py < A.H - 2 && depthp > SD_EPS_F) {  // PM.cc:659-662 (`< 1e-6 -> continue`)
-        const float xp0 = ((float)px - A.cx) / A.fx, xp1 = ((float)py - A.cy) / A.fy;
-        const float dp = 1 / depthp;
-        // operator/(MatExpr, double): alpha = 1./s, which hal::gemm32f(float alpha) rounds to float
-        const double inv_dp = (double)(float)(1.0 / (double)depthp);
-        int nkf = 0;
-        double sJr = 0.0, sJJ = 0.0;
-        for (int j = 0; j < A.n; ++j) {
-            const InterNbr& N = A.nb[j];
-            // temp = gemm(Rji, xp, 1/depthp, tji, 1); Xj = K*temp (small path, float left to right)
-            const float q0 = N.R[0] * xp0 + N.R[1] * xp1 + N.R[2] * 1.0f;
-            const float q1 = N.R[3] * xp0 + N.R[4] * xp1 + N.R[5] * 1.0f;
-            const float q2 = N.R[6] * xp0 + N.R[7] * xp1 + N.R[8] * 1.0f;
-            const float t0 = (float)((double)q0 * inv_dp + (double)N.t[0]);
-            const float t1 = (float)((double)q1 * inv_dp + (double)N.t[1]);
-            const float t2 = (float)((double)q2 * inv_dp + (double)N.t[2]);
-            const float X0 = N.fx * t0 + 0.0f * t1 + N.cx * t2;
-            const float X1 = 0.0f * t0 + N.fy * t1 + N.cy * t2;
-            const float X2 = 0.0f * t0 + 0.0f * t1 + 1.0f * t2;
-            const float inv = (float)(1.0 / (double)X2);  // Xj/Xj(2): convertTo with alpha = 1./s
-            const float xj = X0 * inv, yj = X1 * inv;
-            // Eq. 12, PM.cc:684-688
-            const double rz_d = __fma_rn((double)N.R[8], 1.0, __fma_rn((double)N.R[7], (double)xp1, (double)N.R[6] * (double)xp0));
-            const float rz = (float)rz_d;
-            const float depthj = depthp / (rz + depthp * N.t[2]);
-            if (!(xj >= 0 && xj < (float)(A.W - 1) && yj >= 0 && yj < (float)(A.H - 1))) continue;  // PM.cc:695
-            const int x0 = (int)floorf(xj), y0 = (int)floorf(yj);
+        __syncthreads();
+        // ---- checking stage over the list (tile + 1-pixel halo, image interior only) ----
+        const float thr = A.chi_fuse, thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
+        for (int k = tid; k < n; k += K23_THREADS) {
+            const int i = s_list[k];
+            const int r = i / K23_IW, c = i - r * K23_IW;
+            const int y = y0 + r, x = x0 + c;
+            if (r < 1 || r > K23_IH - 2 || c < 1 || c > K23_IW - 2) continue;
+            if (x < A.border || x >= A.W - A.border || y < A.border || y >= A.H - A.border) continue;
+            const float dc = s_d[i], sc = s_s[i];
+            const float qc = sc * sc, rc = s_rq[i];
+            // compatible neighbours in raster order, then the pixel itself (PM.cc:504-522), fused by GetFusion
+            float pjsj = 0, rsj = 0, min_sigma = 0;
             int ncomp = 0;
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {  // taps (y0,x0) (y1,x0) (y0,x1) (y1,x1), PM.cc:705-752
-                const int ty = y0 + (t & 1), tx = x0 + (t >> 1);
-                const size_t q = (size_t)ty * A.pitch_f + tx;
-                const float d = __ldg(N.depth + q);
+            for (int t = 0; t < 9; ++t) {
+                if (t == 4) continue;
+                const int j = i + (t / 3 - 1) * K23_IW + (t % 3 - 1);
+                const float d = s_d[j];
                 if (d > SD_EPS_F) {
-                    const float s = __ldg(N.sigma + q);
-                    const double dd = (double)(depthj - d);
-                    const float test = (float)((dd * dd) / ((double)s * (double)s));
-                    if (test < A.chi_inter) {
+                    const float s = s_s[j];
+                    if (chi_test_q(d, dc, s * s, qc, s_rq[j], rc, thr, thr_lo, thr_hi)) {
+                        pjsj = (float)((double)pjsj + s_dq[j]);
+                        rsj = (float)((double)rsj + s_r[j]);
+                        // temp_min_sigma starts at compatible_ho[0].sigma; pow(s,2) < pow(min,2) in double
+                        // (exact squares) <=> |s| < |min|
+                        if (ncomp == 0 || fabsf(s) < fabsf(min_sigma)) min_sigma = s;
                         ++ncomp;
-                        // Gauss-Newton terms, PM.cc:777-783 (order: neighbour j, then tap n)
-                        const float djn = 1 / d;
-                        const float d2sigma = djn * djn * s;
-                        const float Jn = -rz / d2sigma;
-                        const float rn = (djn - dp * rz - N.t[2]) / d2sigma;
-                        sJr = __fma_rn((double)Jn, (double)rn, sJr);
-                        sJJ = __fma_rn((double)Jn, (double)Jn, sJJ);
                     }
                 }
             }
-            if (ncomp >= 1) ++nkf;
+            pjsj = (float)((double)pjsj + s_dq[i]);
+            rsj = (float)((double)rsj + s_r[i]);
+            if (ncomp == 0 || fabsf(sc) < fabsf(min_sigma)) min_sigma = sc;
+            ++ncomp;
+            if (ncomp >= 3) {
+                s_d2[i] = pjsj / rsj;
+                s_s2[i] = min_sigma;  // PM.cc:531: min sigma, not the fused sigma
+            } else {
+                s_d2[i] = 0.0f;
+                s_s2[i] = 0.0f;
+            }
         }
-        if (nkf < A.lambdaN) {
-            out = 0.0f;  // sigma untouched, PM.cc:764
+        __syncthreads();
+    }
+
+    // ---- growing stage + outputs: 4 consecutive pixels of one tile row per thread ----
+    const int trow = tid >> 4, tcol = (tid & 15) * 4;
+    const int y = y0 + 2 + trow, xb = x0 + 2 + tcol;
+    float od[4], os[4];
+    int nvalid = 0;
+    uint32_t ventry[4];
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+        const int i = (trow + 2) * K23_IW + tcol + 2 + p;
+        const int x = xb + p;
+        float dn = s_d2[i], sn = s_s2[i];
+        const bool inimg = x < A.W && y < A.H;
+        if (GROW && inimg && x >= A.border && x < A.W - A.border && y >= A.border && y < A.H - A.border && dn <= SD_EPS_F &&
+            sn != 0.0f) {  // sigma == 0: chi = +inf / NaN for every neighbour, nothing to grow (see above)
+            if (!(__ldg(A.grad + (size_t)y * A.pitch_in + x) < A.lambdaG)) {
+                float pjsj = 0, rsj = 0, min_sigma = 0;
+                int nsup = 0;
+                for (int t = 0; t < 9; ++t) {
+                    if (t == 4) continue;
+                    const int j = i + (t / 3 - 1) * K23_IW + (t % 3 - 1);
+                    const float d = s_d2[j], s = s_s2[j];
+                    if (chi_test(d, dn, s, sn, A.chi_fuse)) {
+                        // GetFusion(pairs), PM.cc:926-945
+                        const double sq = (double)s * (double)s;
+                        pjsj = (float)((double)pjsj + (double)d / sq);
+                        rsj = (float)((double)rsj + 1.0 / sq);
+                        if (nsup == 0 || s < min_sigma) min_sigma = s;
+                        ++nsup;
+                    }
+                }
+                if (nsup >= 2) {
+                    dn = pjsj / rsj;
+                    sn = min_sigma;
+                }
+            }
+        }
+        od[p] = dn; os[p] = sn;
+        if (inimg && x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2 && dn > SD_EPS_F) ventry[nvalid++] = ((uint32_t)y << 16) | (uint32_t)x;
+    }
+    if (y < A.H) {
+        const size_t o = (size_t)y * A.pitch_out + xb;
+        if (A.vec_ok && xb + 3 < A.W) {
+            *reinterpret_cast<float4*>(A.depth_out + o) = make_float4(od[0], od[1], od[2], od[3]);
+            *reinterpret_cast<float4*>(A.sigma_out + o) = make_float4(os[0], os[1], os[2], os[3]);
+            if (A.depth_copy) *reinterpret_cast<float4*>(A.depth_copy + o) = make_float4(od[0], od[1], od[2], od[3]);
         } else {
-            const float Jtr0 = (float)(sJr * -1.0);
-            const float JtJ = (float)(sJJ * 1.0);
-            const float dpDelta = Jtr0 / JtJ;
-            out = 1 / (dp + dpDelta);  // PM.cc:793
+            for (int p = 0; p < 4; ++p)
+                if (xb + p < A.W) {
+                    A.depth_out[o + p] = od[p];
+                    A.sigma_out[o + p] = os[p];
+                    if (A.depth_copy) A.depth_copy[o + p] = od[p];
+                }
         }
+    }
+    if (A.vlist) {  // block-wide compaction of the valid pixels: warp scan, one atomicAdd per block
+        int incl = nvalid;
+#pragma unroll
+        for (int dlt = 1; dlt < 32; dlt <<= 1) {
+            const int v = __shfl_up_sync(full, incl, dlt);
+            if (lane >= dlt) incl += v;
+        }
+        if (lane == 31) s_wcnt[wid] = incl;
+        __syncthreads();
+        if (tid == 0) {
+            int tot = 0;
+            for (int w = 0; w < K23_THREADS / 32; ++w) {
+                const int cw = s_wcnt[w];
+                s_wcnt[w] = tot;
+                tot += cw;
+            }
+            s_vbase = tot ? atomicAdd(A.vcount, tot) : 0;
+        }
+        __syncthreads();
+        int pos = s_vbase + s_wcnt[wid] + incl - nvalid;
+        for (int p = 0; p < nvalid; ++p) A.vlist[pos + p] = ventry[p];
+    }
+}
+
+// valid-pixel list of a depth plane that did not come out of k23_intra (sd_import_maps)
+__global__ void __launch_bounds__(256) k_build_vlist(const float* __restrict__ depth, int pitch_f, int W, int H,
+                                                     uint32_t* __restrict__ vlist, int* __restrict__ vcount) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    const bool v = x >= 2 && x < W - 2 && y >= 2 && y < H - 2 && depth[(size_t)y * pitch_f + x] > SD_EPS_F;
+    const unsigned bal = __ballot_sync(0xffffffffu, v);
+    int base = 0;
+    if ((threadIdx.x & 31) == 0 && bal) base = atomicAdd(vcount, __popc(bal));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (v) vlist[base + __popc(bal & ((1u << (threadIdx.x & 31)) - 1u))] = ((uint32_t)y << 16) | (uint32_t)x;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4: InterKeyFrameDepthChecking, PM.cc:628-799, snapshot semantics.  One thread per
+// entry of the valid-pixel list (the pixels PM.cc:662 does not skip); `depth_out` already holds a
+// copy of `depth_in`, so only these pixels are written.
+//
+// Arithmetic notes (all bit-exact with the reference's OpenCV expressions):
+//  * (float)(1.0 / (double)x) == 1.0f / x: rounding a double-rounded quotient of floats to float is
+//    innocuous (53 >= 2*24 + 2 bits), so the reciprocals OpenCV takes in double are IEEE float divisions.
+//  * the chi-square statistic of PM.cc:709-710, (float)(pow(dj - d, 2) / pow(sigma, 2)) < 3.84, is decided
+//    from a float estimate (relative error < 4e-7) unless it lies within 1e-5 of the threshold or an
+//    operand is tiny; then the double expression itself is evaluated.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) k4_inter_check(const __grid_constant__ InterArgs A) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= *A.vcount) return;
+    const uint32_t ent = A.vlist[e];
+    const int px = (int)(ent & 0xffffu), py = (int)(ent >> 16);
+    const size_t o = (size_t)py * A.pitch_f + px;
+    const float depthp = A.depth_in[o];
+    const float xp0 = ((float)px - A.cx) / A.fx, xp1 = ((float)py - A.cy) / A.fy;
+    const float dp = 1 / depthp;
+    // operator/(MatExpr, double): alpha = 1./s, which hal::gemm32f(float alpha) rounds to float
+    const double inv_dp = (double)dp;
+    const double xp0d = (double)xp0, xp1d = (double)xp1;
+    const float thr = A.chi_inter, thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
+    int nkf = 0;
+    double sJr = 0.0, sJJ = 0.0;
+    for (int j = 0; j < A.n; ++j) {
+        const InterNbr& N = A.nb[j];
+        // temp = gemm(Rji, xp, 1/depthp, tji, 1); Xj = K*temp (small path, float left to right)
+        const float q0 = N.R[0] * xp0 + N.R[1] * xp1 + N.R[2] * 1.0f;
+        const float q1 = N.R[3] * xp0 + N.R[4] * xp1 + N.R[5] * 1.0f;
+        const float q2 = N.R[6] * xp0 + N.R[7] * xp1 + N.R[8] * 1.0f;
+        const float t0 = (float)__fma_rn((double)q0, inv_dp, N.td[0]);
+        const float t1 = (float)__fma_rn((double)q1, inv_dp, N.td[1]);
+        const float t2 = (float)__fma_rn((double)q2, inv_dp, N.td[2]);
+        const float X0 = N.fx * t0 + 0.0f * t1 + N.cx * t2;
+        const float X1 = 0.0f * t0 + N.fy * t1 + N.cy * t2;
+        const float X2 = 0.0f * t0 + 0.0f * t1 + 1.0f * t2;
+        const float inv = 1.0f / X2;  // Xj/Xj(2): convertTo with alpha = 1./s
+        const float xj = X0 * inv, yj = X1 * inv;
+        if (!(xj >= 0 && xj < (float)(A.W - 1) && yj >= 0 && yj < (float)(A.H - 1))) continue;  // PM.cc:695
+        // Eq. 12, PM.cc:684-688
+        const float rz = (float)(N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d));
+        const float depthj = depthp / (rz + depthp * N.t[2]);
+        const int x0 = (int)xj, y0 = (int)yj;  // floor of a non-negative float
+        const float* dpl = N.depth + (size_t)y0 * A.pitch_f + x0;
+        const float* spl = N.sigma + (size_t)y0 * A.pitch_f + x0;
+        const float d00 = __ldg(dpl), d10 = __ldg(dpl + A.pitch_f), d01 = __ldg(dpl + 1), d11 = __ldg(dpl + A.pitch_f + 1);
+        int ncomp = 0;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {  // taps (y0,x0) (y1,x0) (y0,x1) (y1,x1), PM.cc:705-752
+            const float d = t == 0 ? d00 : (t == 1 ? d10 : (t == 2 ? d01 : d11));
+            if (d > SD_EPS_F) {
+                const float s = __ldg(spl + (t & 1) * A.pitch_f + (t >> 1));
+                const float dl = depthj - d;
+                const float nf = dl * dl, qf = s * s;
+                const float est = __fdividef(nf, qf);
+                bool comp;
+                if (fminf(nf, qf) > 1e-30f && est < thr_lo) comp = true;
+                else if (fminf(nf, qf) > 1e-30f && est > thr_hi) comp = false;
+                else {
+                    const double dd = (double)dl;
+                    comp = (float)((dd * dd) / ((double)s * (double)s)) < thr;
+                }
+                if (comp) {
+                    ++ncomp;
+                    // Gauss-Newton terms, PM.cc:777-783 (order: neighbour j, then tap n)
+                    const float djn = 1 / d;
+                    const float d2sigma = djn * djn * s;
+                    const float Jn = -rz / d2sigma;
+                    const float rn = (djn - dp * rz - N.t[2]) / d2sigma;
+                    sJr = __fma_rn((double)Jn, (double)rn, sJr);
+                    sJJ = __fma_rn((double)Jn, (double)Jn, sJJ);
+                }
+            }
+        }
+        if (ncomp >= 1) ++nkf;
+    }
+    float out;
+    if (nkf < A.lambdaN) {
+        out = 0.0f;  // sigma untouched, PM.cc:764
+    } else {
+        const float Jtr0 = (float)(sJr * -1.0);
+        const float JtJ = (float)(sJJ * 1.0);
+        const float dpDelta = Jtr0 / JtJ;
+        out = 1 / (dp + dpDelta);  // PM.cc:793
     }
     A.depth_out[o] = out;
 }

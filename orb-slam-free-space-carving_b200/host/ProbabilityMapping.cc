@@ -222,7 +222,7 @@ void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
           "sd_download");
 }
 
-bool ProbabilityMapping::SavePointCloudObj(const std::string& path) {
+bool ProbabilityMapping::SavePointCloudObj(const std::string& path, double max_sigma) {
     std::FILE* f = std::fopen(path.c_str(), "w");
     if (!f) {
         std::fprintf(stderr, "Failed to save points on line\n");  // PM.cc:103
@@ -237,7 +237,7 @@ bool ProbabilityMapping::SavePointCloudObj(const std::string& path) {
         for (int y = 0; y < rows; y++)
             for (int x = 0; x < cols; x++) {
                 const size_t o = (size_t)y * cols + x;
-                if (kf->depth_sigma_[o] > 0.01) continue;
+                if (kf->depth_sigma_[o] > max_sigma) continue;
                 if (kf->depth_map_[o] > 0.000001) {
                     const float* P = &kf->SemiDensePointSets_[(size_t)y * 3 * cols + 3 * x];
                     std::fprintf(f, "v %f %f %f\n", P[0], P[1], P[2]);  // std::to_string(float) == "%f"

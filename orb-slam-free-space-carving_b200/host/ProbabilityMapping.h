@@ -108,8 +108,8 @@ public:
     void UpdateAllSemiDensePointSet();
     void InterKeyFrameDepthChecking(KeyFrameView* currentKf, std::vector<KeyFrameView*> neighbors);
 
-    // PM.cc:100-132: "v x y z" for every pixel with sigma <= 0.01 and inverse depth > 1e-6.
-    bool SavePointCloudObj(const std::string& path);
+    // PM.cc:100-132: "v x y z" for every pixel with sigma <= 0.01 (PM.cc:120) and inverse depth > 1e-6.
+    bool SavePointCloudObj(const std::string& path, double max_sigma = 0.01);
 
     // ComputeFundamental (PM.cc:972-987) and GetRotInPlane + median (PM.cc:467-484, 172-177):
     // private in PM.h, public here so the tests can reach them.

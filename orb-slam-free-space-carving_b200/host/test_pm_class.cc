@@ -2,7 +2,7 @@
 // tests/test_host_class.py, runs ProbabilityMapping::Run() through the class surface and writes the
 // KeyFrameView results back for the Python side to compare with the oracle.
 //
-//   test_pm_class <scene.bin> <out.bin> [obj path]   full run on cuda:0
+//   test_pm_class <scene.bin> <out.bin> [obj path [max sigma]]   full run on cuda:0
 //   test_pm_class --no-device-check                  exits 0 iff construction fails loudly without a GPU
 //
 // scene.bin (little endian): int32 nkf, w, h, covis_n; then per key frame:
@@ -132,7 +132,7 @@ int main(int argc, char** argv) {
             wr(o, rec, 7);
         }
         std::fclose(o);
-        if (argc >= 4 && !pm.SavePointCloudObj(argv[3])) return 1;
+        if (argc >= 4 && !pm.SavePointCloudObj(argv[3], argc >= 5 ? std::atof(argv[4]) : 0.01)) return 1;
         std::printf("ok: %d key frames %dx%d, covisN %d, %d probes\n", nkf, w, h, covis_n, (int)nprobe);
         return 0;
     } catch (const std::exception& e) {
