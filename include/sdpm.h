@@ -128,7 +128,7 @@ int sd_span_begin(sd_ctx* ctx);
 int sd_span_end(sd_ctx* ctx, double* ms);
 /* Per-kernel device timing (CUDA events on the launching stream). enable=1 starts collecting. */
 int sd_timing_enable(sd_ctx* ctx, int enable);
-/* names: "grad", "search", "intra" (checking + growing, one kernel), "inter", "points"; returns accumulated ms and launches */
+/* names: "grad", "search", "fuse", "intra" (checking + growing, one kernel), "inter", "points"; returns accumulated ms and launches */
 int sd_timing_get(sd_ctx* ctx, const char* name, double* ms, uint64_t* launches);
 int sd_timing_reset(sd_ctx* ctx);
 
@@ -156,7 +156,8 @@ int sd_intra_depth_grow_planes(sd_ctx* ctx, float* depth, float* sigma, const fl
 
 /* ---- single-pixel probes (run the same device code as the batch kernels; for unit tests) ---- */
 /* EpipolarSearch PM.cc:385-465 for n pixels xy[2*i], xy[2*i+1] of kf1 against kf2.
- * out[4*i..] = {inverse depth, sigma, best integer uj (or -1), supported} */
+ * out[6*i..] = {inverse depth, sigma, best integer uj (or -1), supported, best_u (the refined u*, PM.cc:459),
+ *               best_v (PM.cc:460)} */
 int sd_probe_epipolar(sd_ctx* ctx, int kf1, int kf2, const int* xy, int n, float min_invdepth, float max_invdepth,
                       float rot_deg, float* out);
 /* InverseDepthHypothesisFusion PM.cc:598-626 on one hypothesis list (n <= SD_MAX_NEIGHBOURS). */

@@ -280,7 +280,7 @@ class Context:
 
     def timing(self):
         out = {}
-        for name in ("grad", "search", "intra", "inter", "points"):
+        for name in ("grad", "search", "fuse", "intra", "inter", "points"):
             ms, n = C.c_double(), C.c_uint64()
             self._ck(self.L.sd_timing_get(self.h, name.encode(), C.byref(ms), C.byref(n)))
             out[name] = (ms.value, n.value)
@@ -299,7 +299,7 @@ class Context:
     def probe_epipolar(self, kf1, kf2, xy, min_depth, max_depth, rot):
         xy, xp = _i(np.asarray(xy).reshape(-1))
         n = len(xy) // 2
-        out = np.empty((n, 4), np.float32)
+        out = np.empty((n, 6), np.float32)
         self._ck(self.L.sd_probe_epipolar(self.h, int(kf1), int(kf2), xp, n, float(min_depth), float(max_depth), float(rot),
                                           out.ctypes.data_as(_fp)))
         return out

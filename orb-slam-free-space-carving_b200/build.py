@@ -59,7 +59,7 @@ def build_sdpm(force=False):
     out = os.path.join(LIB, "libsdpm.so")
     if force or _newer(out, srcs + [__file__]):
         os.makedirs(LIB, exist_ok=True)
-        _run([nvcc_path()] + NVCC_FLAGS + ["-shared", "-o", out, os.path.join(csrc, "sdpm_api.cu")], "libsdpm.build.log")
+        _run([nvcc_path()] + NVCC_FLAGS + os.environ.get("SDPM_NVCC_EXTRA", "").split() + ["-shared", "-o", out, os.path.join(csrc, "sdpm_api.cu")], "libsdpm.build.log")
     return out
 
 

@@ -20,8 +20,8 @@ using namespace sdpm;
 
 namespace {
 
-enum { T_GRAD = 0, T_SEARCH, T_INTRA, T_INTER, T_POINTS, T_COUNT };
-const char* kTimerNames[T_COUNT] = {"grad", "search", "intra", "inter", "points"};
+enum { T_GRAD = 0, T_SEARCH, T_FUSE, T_INTRA, T_INTER, T_POINTS, T_COUNT };
+const char* kTimerNames[T_COUNT] = {"grad", "search", "fuse", "intra", "inter", "points"};
 
 struct Slot {
     int id = -1;
@@ -57,7 +57,9 @@ struct sd_ctx {
     cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
-    float *tmp_depth = nullptr, *tmp_sigma = nullptr;
+    float *tmp_depth = nullptr, *tmp_sigma = nullptr;  // k1_fuse output / k23_intra input
+    float2* hyp = nullptr;                             // hypothesis buffer of k1_search, [neighbour][hyp_stride]
+    int hyp_stride = 0, hyp_rows = 0;
     std::string err;
     uint64_t launches = 0;
     bool timing = false;
@@ -253,7 +255,7 @@ void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
     A.list = s->list; A.meta = s->meta;
     A.count_override = -1;
     A.task_counter = &s->meta->k1_task;
-    A.depth = s->depth; A.sigma = s->sigma;
+    A.hyp = nullptr; A.hyp_stride = 0;
     A.probe_out = nullptr;
 }
 
@@ -261,6 +263,9 @@ void fill_nbr(Slot* s, Slot* nb, float rot, NbrConst& N) {
     geom::fundamental(s->K, s->Rcw, s->tcw, nb->K, nb->Rcw, nb->tcw, N.F);
     geom::relative_pose(s->Rcw, s->tcw, nb->Rcw, nb->tcw, N.R, N.t);
     N.rot = rot;
+    for (int k = 0; k < 3; ++k) { N.Rd0[k] = (double)N.R[k]; N.Rd2[k] = (double)N.R[6 + k]; }
+    N.td0 = (double)N.t[0];
+    N.td2 = (double)N.t[2];
     N.img = nb->gray; N.grad = nb->grad; N.theta = nb->theta; N.arc = nb->arc; N.meta = nb->meta;
 }
 
@@ -336,6 +341,7 @@ int sd_destroy(sd_ctx* c) {
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     cudaFree(c->tmp_depth);
     cudaFree(c->tmp_sigma);
+    cudaFree(c->hyp);
     if (c->ev_tmp) cudaEventDestroy(c->ev_tmp);
     if (c->ev_span_a) cudaEventDestroy(c->ev_span_a);
     if (c->ev_span_b) cudaEventDestroy(c->ev_span_b);
@@ -385,6 +391,19 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     A.n = n;
     A.mind = min_invdepth;
     A.maxd = max_invdepth;
+    A.mind_d = (double)min_invdepth;
+    A.maxd_d = (double)max_invdepth;
+    if (c->hyp_rows < n) {  // grow-only scratch: n x (W*H) hypotheses
+        CU(c, cudaStreamSynchronize(c->s_main));
+        cudaFree(c->hyp);
+        c->hyp = nullptr;
+        c->hyp_rows = 0;
+        c->hyp_stride = (int)align_up((size_t)c->W * c->H, 64);
+        CU(c, cudaMalloc(&c->hyp, (size_t)n * c->hyp_stride * sizeof(float2)));
+        c->hyp_rows = n;
+    }
+    A.hyp = c->hyp;
+    A.hyp_stride = c->hyp_stride;
     CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
@@ -402,11 +421,20 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     CU(c, cudaMemsetAsync(c->tmp_depth, 0, fplane, c->s_main));
     CU(c, cudaMemsetAsync(c->tmp_sigma, 0, fplane, c->s_main));
     CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int) + sizeof(int), c->s_main));  // + valid_count
-    A.depth = c->tmp_depth;
-    A.sigma = c->tmp_sigma;
     {
         ScopedTimer t(c, c->s_main, T_SEARCH);
         k1_search<<<c->k1_grid, K1_WARPS * 32, 0, c->s_main>>>(A);
+    }
+    {
+        ScopedTimer t(c, c->s_main, T_FUSE);
+        FuseArgs F;
+        F.n = n; F.lambdaN = c->P.lambdaN; F.pitch_f = c->pitch_f; F.hyp_stride = c->hyp_stride; F.chi_fuse = c->chi_fuse_f;
+        F.hyp = c->hyp; F.list = s->list; F.meta = s->meta; F.depth = c->tmp_depth; F.sigma = c->tmp_sigma;
+        const int blocks = ((c->W - 2 * c->P.border) * (c->H - 2 * c->P.border) + 127) / 128;  // the list's capacity
+        if (n <= 6) k1_fuse<6><<<blocks, 128, 0, c->s_main>>>(F);
+        else if (n <= 10) k1_fuse<10><<<blocks, 128, 0, c->s_main>>>(F);
+        else if (n <= 16) k1_fuse<16><<<blocks, 128, 0, c->s_main>>>(F);
+        else k1_fuse<SD_MAX_NEIGHBOURS><<<blocks, 128, 0, c->s_main>>>(F);
     }
     {
         ScopedTimer t(c, c->s_main, T_INTRA);
@@ -847,7 +875,7 @@ int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float m
     uint32_t* d_list = nullptr;
     float* d_out = nullptr;
     CU(c, cudaMalloc(&d_list, (n + 1) * sizeof(uint32_t)));  // + the task counter
-    CU(c, cudaMalloc(&d_out, (size_t)n * 4 * sizeof(float)));
+    CU(c, cudaMalloc(&d_out, (size_t)n * 6 * sizeof(float)));
     CU(c, cudaStreamSynchronize(c->s_up));
     CU(c, cudaMemcpyAsync(d_list, entries.data(), n * sizeof(uint32_t), cudaMemcpyHostToDevice, c->s_main));
     static thread_local SearchArgs A;
@@ -855,6 +883,8 @@ int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float m
     A.n = 1;
     A.mind = min_invdepth;
     A.maxd = max_invdepth;
+    A.mind_d = (double)min_invdepth;
+    A.maxd_d = (double)max_invdepth;
     A.list = d_list;
     A.count_override = n;
     A.task_counter = d_list + n;
@@ -865,7 +895,7 @@ int sd_probe_epipolar(sd_ctx* c, int kf1, int kf2, const int* xy, int n, float m
     k1_search<<<blocks, K1_WARPS * 32, 0, c->s_main>>>(A);
     c->launches++;
     CU(c, cudaGetLastError());
-    CU(c, cudaMemcpyAsync(out, d_out, (size_t)n * 4 * sizeof(float), cudaMemcpyDeviceToHost, c->s_main));
+    CU(c, cudaMemcpyAsync(out, d_out, (size_t)n * 6 * sizeof(float), cudaMemcpyDeviceToHost, c->s_main));
     CU(c, cudaStreamSynchronize(c->s_main));
     cudaFree(d_list);
     cudaFree(d_out);

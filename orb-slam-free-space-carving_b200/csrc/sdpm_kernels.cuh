@@ -1,7 +1,8 @@
 // CUDA kernels (sm_100a) of the semi-dense probability-mapping path.
 //
 //   K0 k0_gradient     image -> GradImg / GradTheta / orientation-arc bit planes / active-pixel list / I_stddev sums
-//   K1 k1_search       per active pixel: EpipolarSearch in N neighbours + InverseDepthHypothesisFusion
+//   K1 k1_search       per active pixel: EpipolarSearch in N neighbours -> hypothesis buffer
+//      k1_fuse         per active pixel: InverseDepthHypothesisFusion of its hypotheses -> (depth, sigma) maps
 //   K2+K3 k23_intra    IntraKeyFrameDepthChecking + IntraKeyFrameDepthGrowing (3x3 chi-square stencils,
 //                      one pass) + the valid-pixel list K4 consumes
 //   K4 k4_inter_check  InterKeyFrameDepthChecking           (projection into N neighbours + Gauss-Newton)
@@ -39,6 +40,8 @@ struct NbrConst {  // per neighbour, warp-uniform, lives in kernel parameter (co
     float R[9];    // R21, PM.cc:890
     float t[3];    // t21, PM.cc:891
     float rot;     // median in-plane rotation, degrees, PM.cc:170-179
+    double Rd0[3], Rd2[3];  // rows 0 and 2 of R21 as doubles (double-accumulated dot products, PM.cc:866-868)
+    double td0, td2;        // t21[0], t21[2] as doubles (gemm beta*C epilogue, PM.cc:894-895)
     const uint8_t* img;
     const float* grad;
     const float* theta;
@@ -54,6 +57,7 @@ struct SearchArgs {
     float mind, maxd;  // StereoSearchConstraints interval (inverse depth; mind is the larger), PM.cc:381-382
     float lambdaG, lambdaL, lambdaTheta, slope;
     float chi_fuse;  // smallest float >= 5.99: `chi < 5.99` (float vs double literal) == `chi < chi_fuse`
+    double mind_d, maxd_d;    // the same as doubles (gemm alpha)
     double inv_THETA, THETA;  // 1/THETA and THETA (PM.h:47) as doubles
     const uint8_t* img;
     const float* grad;
@@ -62,9 +66,9 @@ struct SearchArgs {
     const KfMeta* meta;
     int count_override;  // >= 0: use instead of meta->active_count (probes)
     unsigned int* task_counter;  // zeroed before the launch; warps draw 32-entry tasks from it
-    float* depth;
-    float* sigma;
-    float* probe_out;  // nullable; [entry][4] = {rho, sigma, best uj, supported} of neighbour 0
+    float2* hyp;       // nullable; hypothesis buffer [neighbour][hyp_stride]: (rho, sigma), or (-1, 0) for none
+    int hyp_stride;
+    float* probe_out;  // nullable; [entry][6] = {rho, sigma, best uj, supported, best_u, best_v} of neighbour 0
     NbrConst nb[SD_MAX_NEIGHBOURS];
 };
 
@@ -352,21 +356,35 @@ __device__ __forceinline__ bool orientation_gates(float T2, float th_epi, float 
     return !(d > lambdaL) && !(e > lambdaTheta);
 }
 
-// row index of candidate column u on the epipolar line: vj = -(int)((a/b)*uj + c/b), PM.cc:407.
-// Returns ti = -vj.  Rounding is monotone, so ti is monotone in u: the columns that share a row are
-// one contiguous run.  (__float2int_rz saturates; NaN -> 0, which is an invalid row.)
-__device__ __forceinline__ int line_row_neg(float ab, float cb, int u) {
-    return __float2int_rz(__fadd_rn(__fmul_rn(ab, (float)u), cb));
+// (float)u for 0 <= u < 2^23 without the conversion pipe: 2^23 + u is exact, so is the subtraction
+__device__ __forceinline__ float small_int_to_float(int u) { return __int_as_float(0x4B000000 | u) - 8388608.0f; }
+
+// Image row of candidate column u on the epipolar line.  The reference computes
+// vj = -(int)((a/b)*uj + c/b) (PM.cc:407) and rejects vj <= 0 || vj >= rows (PM.cc:408).  With
+// vf = (a/b)*uj + c/b this function returns floor(-vf) when |vf| < 2^22 -- equal to vj whenever vj is
+// an admissible row (vf < 0 there) -- and some value outside (0, 65536) for every other vf (vf >= 0,
+// huge, inf, NaN), so `0 < row && row < H` is exactly the reference's admission test.  Adding
+// 1.5*2^23 with round-toward-zero leaves floor(x) in the low mantissa bits of a positive sum; no
+// float<->int conversion instruction is needed.  The row is monotone in u, so the columns that
+// share a row form one contiguous run.
+__device__ __forceinline__ int line_row(float ab, float cb, float uf, float& vf) {
+    vf = __fadd_rn(__fmul_rn(ab, uf), cb);
+    return __float_as_int(__fadd_rz(-vf, 12582912.0f)) - 0x4B400000;
+}
+__device__ __forceinline__ int line_row(float ab, float cb, int u) {
+    float vf;
+    return line_row(ab, cb, small_int_to_float(u), vf);
 }
 
-// largest u1 in [u, ue) whose row equals t0; precondition line_row_neg(u) == t0 != line_row_neg(ue).
+// largest u1 in [u, ue) whose row equals r0; precondition line_row(u) == r0 != line_row(ue).
 // The division-based estimate only decides where the exact search starts.
-__device__ __forceinline__ int run_end(float ab, float cb, float inv_ab, int u, int ue, int t0) {
-    const float bv = (float)t0 + ((ab > 0.f) ? (t0 < 0 ? 0.f : 1.f) : (t0 <= 0 ? -1.f : 0.f));
+__device__ __forceinline__ int run_end(float ab, float cb, float inv_ab, int u, int ue, int r0) {
+    // the row changes where ab*u + cb crosses -r0 (ab > 0: row decreases) or -(r0 + 1) (ab < 0)
+    const float bv = -(float)r0 - ((ab > 0.f) ? 0.f : 1.f);
     const float uc = (bv - cb) * inv_ab;
     int u1 = (uc >= (float)u) ? ((uc < (float)ue) ? (int)uc : ue - 1) : u;  // NaN -> u
-    while (u1 > u && line_row_neg(ab, cb, u1) != t0) --u1;
-    while (u1 + 1 < ue && line_row_neg(ab, cb, u1 + 1) == t0) ++u1;
+    while (u1 > u && line_row(ab, cb, u1) != r0) --u1;
+    while (u1 + 1 < ue && line_row(ab, cb, u1 + 1) == r0) ++u1;
     return u1;
 }
 
@@ -382,7 +400,7 @@ __device__ __noinline__ int exact_line_scan(const SearchArgs& A, const NbrConst&
     float best = 1000000.0f;
     int bj = -1;
     for (int uj = L.u_lo; uj <= L.u_hi; ++uj) {
-        const int ti = line_row_neg(L.ab, L.cb, uj);
+        const int ti = __float2int_rz(__fadd_rn(__fmul_rn(L.ab, (float)uj), L.cb));
         if (!(ti < 0 && ti > -A.H)) continue;  // PM.cc:408
         const size_t o = (size_t)(-ti) * A.pitch_f + min(uj, A.W - 1);
         if (__ldg(N.grad + o) < A.lambdaG) continue;  // PM.cc:411
@@ -411,39 +429,51 @@ __device__ __forceinline__ bool chi_test_q(float a, float b, float qa, float qb,
     return num / qa + num / qb < thr;
 }
 
-// InverseDepthHypothesisFusion, PM.cc:598-626 (+ ChiTest 912-924, GetFusion 947-970) on the nh
-// hypotheses of one pixel.  ChiTest is symmetric in (a, b) (the squared difference and the float
-// sum commute), so each unordered pair is tested once.  Returns false when unsupported.
-__device__ __forceinline__ bool fuse_hypotheses(const float* hd, const float* hs, int nh, int lambdaN, float thr, float& out_d, float& out_s) {
-    float hq[SD_MAX_NEIGHBOURS], hr[SD_MAX_NEIGHBOURS];
-    unsigned char cnt[SD_MAX_NEIGHBOURS];
+// InverseDepthHypothesisFusion, PM.cc:598-626 (+ ChiTest 912-924, GetFusion 947-970) on up to NT
+// hypothesis slots of one pixel; slot i is a hypothesis iff bit i of `present` is set (the reference's
+// vector holds the present ones in the same order, so "first largest set" and the accumulation order
+// are unchanged).  ChiTest is symmetric in (a, b) (the squared difference and the float sum commute),
+// so each unordered pair is tested once.  NT is a compile-time bound so that the arrays live in
+// registers.  Returns false when unsupported.
+template <int NT>
+__device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const float (&hs)[NT], unsigned long long present, int lambdaN,
+                                                float thr, float& out_d, float& out_s) {
+    float hq[NT], hr[NT];
+    int cnt[NT];
     const float thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
-    for (int i = 0; i < nh; ++i) {
+#pragma unroll(NT <= 16 ? NT : 1)
+    for (int i = 0; i < NT; ++i) {
         const float q = hs[i] * hs[i];
         hq[i] = q;
         hr[i] = 1.0f / q;
         // ChiTest(a, a): num = +0, chi = 0/q + 0/q = 0 unless q is 0 or NaN (then NaN -> false)
         cnt[i] = (q > 0.0f && 0.0f < thr) ? 1 : 0;
     }
-    for (int i = 0; i < nh; ++i) {
-        const float di = hd[i], qi = hq[i], ri = hr[i];
-        int ci = 0;
-        for (int k = i + 1; k < nh; ++k) {
-            if (chi_test_q(di, hd[k], qi, hq[k], ri, hr[k], thr, thr_lo, thr_hi)) {
-                ++ci;
-                cnt[k] = (unsigned char)(cnt[k] + 1);
+#pragma unroll(NT <= 16 ? NT : 1)
+    for (int i = 0; i < NT; ++i) {
+        if (!((present >> i) & 1ull)) continue;
+#pragma unroll(NT <= 16 ? NT : 1)
+        for (int k = i + 1; k < NT; ++k) {
+            if (!((present >> k) & 1ull)) continue;
+            if (chi_test_q(hd[i], hd[k], hq[i], hq[k], hr[i], hr[k], thr, thr_lo, thr_hi)) {
+                ++cnt[i];
+                ++cnt[k];
             }
         }
-        cnt[i] = (unsigned char)(cnt[i] + ci);
     }
     int best_cnt = 0, best_a = -1;
-    for (int i = 0; i < nh; ++i)
-        if ((int)cnt[i] > best_cnt) { best_cnt = cnt[i]; best_a = i; }  // strict >, first largest set wins (PM.cc:616)
+    float da = 0.f, qa = 0.f, ra = 0.f;
+#pragma unroll(NT <= 16 ? NT : 1)
+    for (int i = 0; i < NT; ++i)
+        if (((present >> i) & 1ull) && cnt[i] > best_cnt) {  // strict >, first largest set wins (PM.cc:616)
+            best_cnt = cnt[i]; best_a = i; da = hd[i]; qa = hq[i]; ra = hr[i];
+        }
     if (best_cnt < lambdaN) return false;
     // GetFusion(depthHo), PM.cc:947-970: pow(sigma,2) in double, float accumulators, members in index order
     float pjsj = 0, rsj = 0;
-    const float da = hd[best_a], qa = hq[best_a], ra = hr[best_a];
-    for (int ib = 0; ib < nh; ++ib) {
+#pragma unroll(NT <= 16 ? NT : 1)
+    for (int ib = 0; ib < NT; ++ib) {
+        if (!((present >> ib) & 1ull)) continue;
         const bool comp = (ib == best_a) ? (qa > 0.0f && 0.0f < thr) : chi_test_q(da, hd[ib], qa, hq[ib], ra, hr[ib], thr, thr_lo, thr_hi);
         if (!comp) continue;
         const double s2 = (double)hs[ib] * (double)hs[ib];
@@ -457,6 +487,9 @@ __device__ __forceinline__ bool fuse_hypotheses(const float* hd, const float* hs
 
 constexpr int K1_WARPS = 8;
 constexpr int K1_QCAP = 1024 + 32;  // one scan step queues at most 32 lanes x 32 columns on top of < 32 leftovers
+#ifndef K1_MIN_BLOCKS
+#define K1_MIN_BLOCKS 4
+#endif
 #define K1_TIE_REL 2e-6f            // float shortcut of err: two candidates closer than this are re-scanned exactly
 #define K1_ERR_LIMIT_LO 999000.0f   // PM.cc:437 initial best_match_err = 1e6
 
@@ -466,30 +499,35 @@ constexpr int K1_QCAP = 1024 + 32;  // one scan step queues at most 32 lanes x 3
 //      424-426) and the orientation-arc plane of the neighbour that matches `th_pi + rot`.
 //  (B) per lane: walk the line run by run (a run = consecutive columns on one image row, clipped to
 //      a 32-column word of the bit plane): ONE u32 load yields every column of the run that passes
-//      condition 1 and can pass condition 3.  Selected columns are pushed to a per-warp queue.
+//      condition 1 and can pass condition 3.  Selected columns are appended to a per-warp queue
+//      (positions from a warp prefix sum: no atomics).
 //  (C) whenever 32 are queued they are evaluated one per lane, whichever lane they came from: exact
 //      conditions 2+3 on GradTheta, photometric + gradient residual (PM.cc:433-436) with the err
-//      of PM.cc:436 in float; shared-memory atomicMin keeps the smallest err per owner.  A pixel
+//      of PM.cc:436 in float; a shared-memory atomicMin keeps the smallest err per owner, attempted
+//      only by candidates that are not already beaten by the owner's current best.  A pixel
 //      whose two smallest errs are within K1_TIE_REL of each other is flagged and re-scanned by
 //      exact_line_scan, so the winner is always the one the reference's sequential strict-<
 //      scan picks (smallest err in the reference arithmetic, first column on ties).
-//  (D) per lane: sub-pixel refinement and inverse-depth hypothesis (PM.cc:446-463, 806-829).
-// After the last neighbour: InverseDepthHypothesisFusion (PM.cc:598-626) per lane.
-__global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant__ SearchArgs A) {
+//  (D) per lane: sub-pixel refinement and inverse-depth hypothesis (PM.cc:446-463, 806-829), written
+//      to the hypothesis buffer [neighbour][entry]; k1_fuse turns the buffer into the maps.
+__global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const __grid_constant__ SearchArgs A) {
     __shared__ uint32_t s_queue[K1_WARPS][K1_QCAP];
+    __shared__ float4 s_par4[K1_WARPS][32];  // per owner lane: a/b, c/b, I1, GradImg1
+    __shared__ float2 s_par2[K1_WARPS][32];  // per owner lane: epipolar-line angle, rotated orientation
     __shared__ uint32_t s_beste[K1_WARPS][32];
     __shared__ uint32_t s_bestu[K1_WARPS][32];
-    __shared__ uint32_t s_qn[K1_WARPS];
     __shared__ uint32_t s_tie[K1_WARPS];
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+    const unsigned lt_mask = (1u << lane) - 1u;
     const int count = A.count_override >= 0 ? A.count_override : A.meta->active_count;
 
     uint32_t* queue = s_queue[wib];
     uint32_t* beste = s_beste[wib];
     uint32_t* bestu = s_bestu[wib];
-    volatile uint32_t* qn_s = &s_qn[wib];
+    float4* par4 = s_par4[wib];
+    float2* par2 = s_par2[wib];
     const float colsf = (float)A.W;
     const float inv_theta_f = (float)A.inv_THETA;
     const size_t arc_plane = (size_t)A.H * A.arc_pitch;
@@ -514,9 +552,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
     const float g1 = valid ? __ldg(A.grad + (size_t)y * A.pitch_f + x) : 0.f;         // PM.cc:434
     const float th1 = valid ? __ldg(A.theta + (size_t)y * A.pitch_f + x) : 0.f;       // PM.cc:214
     const float xp0 = (xf - A.cx) / A.fx, xp1 = (yf - A.cy) / A.fy;                   // PM.cc:893, 862
-
-    float hd[SD_MAX_NEIGHBOURS], hs[SD_MAX_NEIGHBOURS];
-    int nh = 0;
+    const double xp0d = (double)xp0, xp1d = (double)xp1;
 
     for (int j = 0; j < A.n; ++j) {
         const NbrConst& N = A.nb[j];
@@ -530,10 +566,11 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
         // xp2 = gemm(R21, xp1, rho, t21, 1): float dot left to right, epilogue in double
         const float q0 = N.R[0] * xp0 + N.R[1] * xp1 + N.R[2] * 1.0f;
         const float q2 = N.R[6] * xp0 + N.R[7] * xp1 + N.R[8] * 1.0f;
-        const float xmin0 = (float)__fma_rn((double)q0, (double)A.mind, (double)N.t[0]);
-        const float xmin2 = (float)__fma_rn((double)q2, (double)A.mind, (double)N.t[2]);
-        const float xmax0 = (float)__fma_rn((double)q0, (double)A.maxd, (double)N.t[0]);
-        const float xmax2 = (float)__fma_rn((double)q2, (double)A.maxd, (double)N.t[2]);
+        const double q0d = (double)q0, q2d = (double)q2;
+        const float xmin0 = (float)__fma_rn(q0d, A.mind_d, N.td0);
+        const float xmin2 = (float)__fma_rn(q2d, A.mind_d, N.td2);
+        const float xmax0 = (float)__fma_rn(q0d, A.maxd_d, N.td0);
+        const float xmax2 = (float)__fma_rn(q2d, A.maxd_d, N.td2);
         float umin = A.fx * xmin0 / xmin2 + A.cx;
         float umax = A.fx * xmax0 / xmax2 + A.cx;
         if (umin > umax) { float t = umax; umax = umin; umin = t; }
@@ -545,8 +582,23 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
         const int u_lo = (int)ceilf(umin);
         const int u_hi = ok ? (int)floorf(umax) : -1;  // candidates: u_lo..u_hi (u_hi may equal W)
 
-        // gate angles, loop invariant: PM.cc:414, 424-426
-        const float th_epi = fast_atan2_deg(-ab, 1.0f);
+        // gate angles, loop invariant: PM.cc:414, 424-426.  th_epi = cv::fastAtan2(-a/b, 1): with x = 1 the
+        // quotient min/(max + DBL_EPSILON) is |a/b| / 1 or 1 / |a/b| exactly (the float sum absorbs the epsilon)
+        const float inv_ab = 1.0f / ab;
+        float th_epi;
+        {
+            const float p1 = 0.9997878412794807f * (float)(180 / 3.14159265358979323846);
+            const float p3 = -0.3258083974640975f * (float)(180 / 3.14159265358979323846);
+            const float p5 = 0.1555786518463281f * (float)(180 / 3.14159265358979323846);
+            const float p7 = -0.04432655554792128f * (float)(180 / 3.14159265358979323846);
+            const float ay = fabsf(ab);
+            const bool shallow = 1.0f >= ay;
+            const float cq = shallow ? ay : fabsf(inv_ab);
+            const float c2 = cq * cq;
+            const float pa = (((p7 * c2 + p5) * c2 + p3) * c2 + p1) * cq;
+            th_epi = shallow ? pa : 90.f - pa;
+            if (-ab < 0) th_epi = 360.f - th_epi;
+        }
         float apr = th1 + N.rot;
         if (apr >= 360) apr -= 360;
         if (apr < 0) apr += 360;
@@ -554,58 +606,60 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
         int cell = SD_ARC_CELLS;
         if (apr >= 0.f && apr < 360.f) cell = min((int)(apr * (1.0f / SD_ARC_CELL_DEG)), SD_ARC_CELLS - 1);
         const uint32_t* __restrict__ arcp = N.arc + (size_t)cell * arc_plane;
-        const float inv_ab = 1.0f / ab;
 
+        par4[lane] = make_float4(ab, cb, I1, g1);
+        par2[lane] = make_float2(th_epi, apr);
         beste[lane] = 0x7f800000u;  // +inf
-        if (lane == 0) { *qn_s = 0; s_tie[wib] = 0; }
+        if (lane == 0) s_tie[wib] = 0;
         __syncwarp();
 
         // ---------------- (C) evaluate queued candidates, one per lane ----------------
-        int qn = 0;
+        int qn = 0;  // warp-uniform
         auto drain = [&](bool all) {
             while (qn >= 32 || (all && qn > 0)) {
                 const int take = min(qn, 32);
                 const int base = qn - take;
                 const bool have = lane < take;
+                bool won = false;
+                uint32_t eb = 0;
                 int owner = lane, uq = 0;
                 if (have) {
                     const uint32_t e = queue[base + lane];
                     owner = (int)(e >> 16);
                     uq = (int)(e & 0xffffu);
-                }
-                const float oab = __shfl_sync(full, ab, owner);
-                const float ocb = __shfl_sync(full, cb, owner);
-                const float oI1 = __shfl_sync(full, I1, owner);
-                const float og1 = __shfl_sync(full, g1, owner);
-                const float oepi = __shfl_sync(full, th_epi, owner);
-                const float oapr = __shfl_sync(full, apr, owner);
-                bool won = false;
-                uint32_t eb = 0;
-                if (have) {
-                    const float vf = __fadd_rn(__fmul_rn(oab, (float)uq), ocb);
-                    const int r0 = -__float2int_rz(vf);  // 0 < r0 < H by construction; == floor(-vf)
+                    const float4 p4 = par4[owner];
+                    const float2 p2 = par2[owner];
+                    float vf;
+                    const int r0 = line_row(p4.x, p4.y, small_int_to_float(uq), vf);  // 0 < r0 < H by construction
                     const int xc = min(uq, A.W - 1);
-                    const int r1 = min(r0 + 1, A.H - 1);
+                    const int dr = (r0 + 1 < A.H) ? 1 : 0;  // second bilinear row clamps to the image (H2)
                     const unsigned of0 = (unsigned)(r0 * A.pitch_f + xc);  // planes hold < 2^31 elements (checked at upload)
+                    const unsigned ob0 = (unsigned)(r0 * A.pitch_u8 + xc);
+                    // all five taps are requested before the gates are known (3 of 4 queued candidates pass them)
                     const float T2 = __ldg(N.theta + of0);
-                    if (orientation_gates(T2, oepi, oapr, A.lambdaL, A.lambdaTheta)) {
+                    const float gg0 = __ldg(N.grad + of0);
+                    const float gg1 = __ldg(N.grad + of0 + (unsigned)(dr * A.pitch_f));
+                    const float i0 = (float)__ldg(N.img + ob0);
+                    const float i1 = (float)__ldg(N.img + ob0 + (unsigned)(dr * A.pitch_u8));
+                    const float cur = __uint_as_float(beste[owner]);
+                    if (orientation_gates(T2, p2.x, p2.y, A.lambdaL, A.lambdaTheta)) {
                         const float yv = -vf;
-                        const float w0 = ((float)r0 + 1.0f) - yv;  // bilinear_col weights, PM.cc:46-53
+                        const float w0 = (small_int_to_float(r0) + 1.0f) - yv;  // bilinear_col weights, PM.cc:46-53
                         const float w1 = 1.0f - w0;
-                        const float i0 = (float)__ldg(N.img + (unsigned)(r0 * A.pitch_u8 + xc));
-                        const float i1 = (float)__ldg(N.img + (unsigned)(r1 * A.pitch_u8 + xc));
-                        const float gg0 = __ldg(N.grad + of0);
-                        const float gg1 = __ldg(N.grad + (unsigned)(r1 * A.pitch_f + xc));
-                        const float rI = oI1 - (i0 * w0 + i1 * w1);
-                        const float rG = og1 - (gg0 * w0 + gg1 * w1);
+                        const float rI = p4.z - (i0 * w0 + i1 * w1);
+                        const float rG = p4.w - (gg0 * w0 + gg1 * w1);
                         const float ef = rI * rI + (rG * rG) * inv_theta_f;  // float shortcut of PM.cc:436
                         if (ef < K1_ERR_LIMIT_LO) {
-                            eb = __float_as_uint(ef);
-                            const uint32_t old = atomicMin(&beste[owner], eb);
-                            const float fo = __uint_as_float(old);
-                            const float lo = fminf(ef, fo), hi = fmaxf(ef, fo);
-                            if (hi - lo <= __fmaf_rn(lo, K1_TIE_REL, 1e-30f)) atomicOr(&s_tie[wib], 1u << owner);
-                            won = eb < old;
+                            // a candidate above the owner's current best by more than the tie band can neither
+                            // win nor tie with the final best (which is <= cur): no atomic needed
+                            if (!(ef > __fmaf_rn(cur, 2.0f * K1_TIE_REL, cur))) {
+                                eb = __float_as_uint(ef);
+                                const uint32_t old = atomicMin(&beste[owner], eb);
+                                const float fo = __uint_as_float(old);
+                                const float lo = fminf(ef, fo), hi = fmaxf(ef, fo);
+                                if (hi - lo <= __fmaf_rn(lo, K1_TIE_REL, 1e-30f)) atomicOr(&s_tie[wib], 1u << owner);
+                                won = eb < old;
+                            }
                         } else {  // never with u8 images (err <= ~2.1e5); keep the 1e6 limit exact anyway
                             atomicOr(&s_tie[wib], 1u << owner);
                         }
@@ -620,15 +674,22 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
 
         // ---------------- (B) run-by-run scan of the arc plane ----------------
         auto push = [&](uint32_t m, int col_base) {
-            int pos = 0;
-            if (m) pos = (int)atomicAdd(&s_qn[wib], (unsigned)__popc(m));
+            const int cnt = __popc(m);
+            int incl = cnt;
+#pragma unroll
+            for (int dlt = 1; dlt < 32; dlt <<= 1) {
+                const int v = __shfl_up_sync(full, incl, dlt);
+                if (lane >= dlt) incl += v;
+            }
+            int pos = qn + incl - cnt;
+            const uint32_t tag = ((uint32_t)lane << 16) | (uint32_t)col_base;
             while (m) {
                 const int bit = __ffs((int)m) - 1;
                 m &= m - 1;
-                queue[pos++] = ((uint32_t)lane << 16) | (uint32_t)(col_base + bit);
+                queue[pos++] = tag + (uint32_t)bit;
             }
+            qn += __shfl_sync(full, incl, 31);
             __syncwarp();
-            qn = (int)*qn_s;
         };
 
         const int u_end = min(u_hi, A.W - 1);
@@ -638,28 +699,28 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
             int col_base = 0;
             if (u <= u_end) {
                 int ue = min(u | 31, u_end);
-                const int t0 = line_row_neg(ab, cb, u);
-                if (ue > u && line_row_neg(ab, cb, ue) != t0) ue = run_end(ab, cb, inv_ab, u, ue, t0);
-                if (t0 < 0 && t0 > -A.H) {  // PM.cc:408: 0 < vj < rows
-                    const uint32_t w = __ldg(arcp + (unsigned)((-t0) * A.arc_pitch + (u >> 5)));
+                const int r0 = line_row(ab, cb, u);
+                if (ue > u && line_row(ab, cb, ue) != r0) ue = run_end(ab, cb, inv_ab, u, ue, r0);
+                if (r0 > 0 && r0 < A.H) {  // PM.cc:408: 0 < vj < rows
+                    const uint32_t w = __ldg(arcp + (unsigned)(r0 * A.arc_pitch + (u >> 5)));
                     m = w & (0xffffffffu << (u & 31)) & (0xffffffffu >> (31 - (ue & 31)));
                 }
                 col_base = u & ~31;
                 u = ue + 1;
             }
-            push(m, col_base);
-            drain(false);
-            if (lane == 0) *qn_s = (uint32_t)qn;
-            __syncwarp();
+            if (__any_sync(full, m != 0u)) {
+                push(m, col_base);
+                drain(false);
+            }
         }
         // candidate column uj == cols reads column cols-1 (clamp-to-edge)
         const bool extra = u_hi >= A.W && u_lo <= A.W;
         if (__any_sync(full, extra)) {
             uint32_t m = 0;
             if (extra) {
-                const int t0 = line_row_neg(ab, cb, A.W);
-                if (t0 < 0 && t0 > -A.H) {
-                    const uint32_t w = __ldg(arcp + (size_t)(-t0) * A.arc_pitch + ((A.W - 1) >> 5));
+                const int r0 = line_row(ab, cb, A.W);
+                if (r0 > 0 && r0 < A.H) {
+                    const uint32_t w = __ldg(arcp + (size_t)r0 * A.arc_pitch + ((A.W - 1) >> 5));
                     m = (w >> ((A.W - 1) & 31)) & 1u;
                 }
             }
@@ -677,7 +738,8 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
         } else if (beste[lane] != 0x7f800000u) {
             bj = (int)bestu[lane];
         }
-        float rho = 0.f, sig = 0.f;
+        float rho = -1.0f, sig = 0.f;  // (-1, 0): "no hypothesis" -- fails the 1/rho > 0 test of PM.cc:216 like any negative rho
+        float best_u = 0.f;
         const bool found = bj >= 0;
         if (found) {
             const float yb = -(ab * (float)bj + cb);
@@ -692,11 +754,12 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
             const double itq = A.inv_THETA * (double)q;                           // (1/THETA)*q
             const float den = (float)((double)(g * g) + itq * (double)q);         // PM.cc:455
             const float ustar = (float)((double)bj + ((double)(g * rI) + itq * (double)rG) / (double)den);  // PM.cc:456
+            best_u = ustar;  // PM.cc:459
             const float istd = N.meta->istddev;
             const float uvar = 2 * istd * istd / den;  // PM.cc:457
             // ComputeInvDepthHypothesis
-            const double d2 = __fma_rn((double)N.R[8], 1.0, __fma_rn((double)N.R[7], (double)xp1, (double)N.R[6] * (double)xp0));
-            const double d0 = __fma_rn((double)N.R[2], 1.0, __fma_rn((double)N.R[1], (double)xp1, (double)N.R[0] * (double)xp0));
+            const double d2 = N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d);
+            const double d0 = N.Rd0[2] + __fma_rn(N.Rd0[1], xp1d, N.Rd0[0] * xp0d);
             const float num2f = (float)(d0 * (double)A.fx);
             const float den2 = A.fx * N.t[0];
             const float sq = sqrtf(uvar);
@@ -705,37 +768,72 @@ __global__ void __launch_bounds__(K1_WARPS * 32) k1_search(const __grid_constant
             const float rmax = pixel_inv_depth(ustar + sq, A.cx, d2, num2f, N.t[2], den2);
             const float e1 = fabsf(rmax - rho), e2 = fabsf(rmin - rho);
             sig = (e1 < e2) ? e2 : e1;  // std::max(e1, e2)
-            if (1 / rho > 0.0f) {       // PM.cc:216
-                hd[nh] = rho;
-                hs[nh] = sig;
-                ++nh;
+        }
+        if (valid) {
+            if (A.hyp) A.hyp[(size_t)j * A.hyp_stride + entry] = make_float2(rho, sig);
+            if (A.probe_out && j == 0) {
+                float* o = A.probe_out + (size_t)entry * 6;
+                o[0] = found ? rho : 0.f; o[1] = sig; o[2] = (float)bj; o[3] = found ? 1.f : 0.f;
+                o[4] = best_u; o[5] = found ? -(ab * best_u + cb) : 0.f;  // PM.cc:459-460
             }
         }
-        if (A.probe_out && j == 0 && valid) {
-            float* o = A.probe_out + (size_t)entry * 4;
-            o[0] = rho; o[1] = sig; o[2] = (float)bj; o[3] = found ? 1.f : 0.f;
-        }
         __syncwarp();
-    }
-
-    // ---------------- InverseDepthHypothesisFusion, PM.cc:221-228 + 598-626 ----------------
-    if (valid && !A.probe_out && nh > A.lambdaN) {
-        float fd, fs;
-        if (fuse_hypotheses(hd, hs, nh, A.lambdaN, A.chi_fuse, fd, fs)) {
-            A.depth[(size_t)y * A.pitch_f + x] = fd;
-            A.sigma[(size_t)y * A.pitch_f + x] = fs;
-        }
     }
   }  // task loop
 }
 
-// fusion probe: one thread, same device function as the tail of k1_search
+// InverseDepthHypothesisFusion over the hypothesis buffer of k1_search, PM.cc:216-228: one thread per
+// active pixel; a hypothesis counts if 1/rho > 0 (PM.cc:216); more than lambdaN of them are fused
+// (PM.cc:221) and the result is stored if supported (PM.cc:224-227).
+struct FuseArgs {
+    int n, lambdaN, pitch_f, hyp_stride;
+    float chi_fuse;
+    const float2* hyp;
+    const uint32_t* list;
+    const KfMeta* meta;
+    float* depth;
+    float* sigma;
+};
+
+template <int NT>
+__global__ void __launch_bounds__(128) k1_fuse(const FuseArgs F) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= F.meta->active_count) return;
+    float hd[NT], hs[NT];
+    unsigned long long present = 0;
+    int nh = 0;
+#pragma unroll(NT <= 16 ? NT : 1)
+    for (int j = 0; j < NT; ++j) {
+        hd[j] = 0.f; hs[j] = 0.f;
+        if (j < F.n) {
+            const float2 h = __ldg(F.hyp + (size_t)j * F.hyp_stride + e);
+            hd[j] = h.x; hs[j] = h.y;
+            if (1 / h.x > 0.0f) { present |= 1ull << j; ++nh; }
+        }
+    }
+    if (nh > F.lambdaN) {
+        float fd, fs;
+        if (fuse_hypotheses<NT>(hd, hs, present, F.lambdaN, F.chi_fuse, fd, fs)) {
+            const uint32_t ent = F.list[e];
+            const size_t o = (size_t)(ent >> 16) * F.pitch_f + (ent & 0xffffu);
+            F.depth[o] = fd;
+            F.sigma[o] = fs;
+        }
+    }
+}
+
+// fusion probe: one thread, same device function as k1_fuse
 __global__ void k1_fusion_probe(const float* d, const float* s, int n, int lambdaN, float chi_fuse, float* out) {
     float hd[SD_MAX_NEIGHBOURS], hs[SD_MAX_NEIGHBOURS];
-    for (int i = 0; i < n; ++i) { hd[i] = d[i]; hs[i] = s[i]; }
+    unsigned long long present = 0;
+    for (int i = 0; i < SD_MAX_NEIGHBOURS; ++i) {
+        hd[i] = i < n ? d[i] : 0.f;
+        hs[i] = i < n ? s[i] : 0.f;
+        if (i < n) present |= 1ull << i;
+    }
     out[0] = out[1] = out[2] = 0.f;
     float fd, fs;
-    if (fuse_hypotheses(hd, hs, n, lambdaN, chi_fuse, fd, fs)) {
+    if (fuse_hypotheses<SD_MAX_NEIGHBOURS>(hd, hs, present, lambdaN, chi_fuse, fd, fs)) {
         out[0] = fd;
         out[1] = fs;
         out[2] = 1.f;

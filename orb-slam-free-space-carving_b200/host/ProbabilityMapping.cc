@@ -129,20 +129,14 @@ void ProbabilityMapping::EpipolarSearch(KeyFrameView* kf1, KeyFrameView* kf2, co
     ensure_uploaded(kf1);
     ensure_uploaded(kf2);
     const int xy[2] = {x, y};
-    float out[4] = {0, 0, -1, 0};
+    float out[6] = {0, 0, -1, 0, 0, 0};
     check(sd_probe_epipolar(ctx_, kf1->mnId, kf2->mnId, xy, 1, min_depth, max_depth, rot, out), "sd_probe_epipolar");
     dh->supported = out[3] != 0.0f;
     if (dh->supported) {
         dh->depth = out[0];
         dh->sigma = out[1];
-        best_u = out[2];
-        // best_v = -((a/b)*best_u + c/b) (PM.cc:441) is debug output only in the reference
-        float F12[9], R21[9], t21[3];
-        check(sd_pair_geometry(kf1->K, kf1->Tcw, kf2->K, kf2->Tcw, F12, R21, t21), "sd_pair_geometry");
-        const float a = x * F12[0] + y * F12[3] + F12[6];
-        const float b = x * F12[1] + y * F12[4] + F12[7];
-        const float c = x * F12[2] + y * F12[5] + F12[8];
-        best_v = -((a / b) * best_u + (c / b));
+        best_u = out[4];  // PM.cc:459-460
+        best_v = out[5];
     }
 }
 

@@ -156,6 +156,7 @@ def test_probe_epipolar_search(pkg, po, synth, pipeline):
                 found += 1
                 assert out[i, 0] == np.float32(rho) and out[i, 1] == np.float32(sig), (i, x, y, out[i], rho, sig)
                 assert 0 <= out[i, 2] <= 640           # winning integer column (the refined u* is unbounded in the reference)
+                assert out[i, 4] == np.float32(bu) and out[i, 5] == np.float32(bv)     # best_u, best_v of PM.cc:459-460
         assert found > 100
     ctx.close()
 
