@@ -486,9 +486,16 @@ __device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const flo
 }
 
 constexpr int K1_WARPS = 8;
-constexpr int K1_QCAP = 1024 + 32;  // one scan step queues at most 32 lanes x 32 columns on top of < 32 leftovers
+constexpr int K1_QHALF = 512;           // what 16 lanes can queue in one scan step (16 lanes x 32 columns)
+constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller step is queued in two halves
+#ifndef K1F_MIN_BLOCKS
+#define K1F_MIN_BLOCKS 8
+#endif
+#ifndef K4_MIN_BLOCKS
+#define K4_MIN_BLOCKS 8
+#endif
 #ifndef K1_MIN_BLOCKS
-#define K1_MIN_BLOCKS 4
+#define K1_MIN_BLOCKS 5
 #endif
 #define K1_TIE_REL 2e-6f            // float shortcut of err: two candidates closer than this are re-scanned exactly
 #define K1_ERR_LIMIT_LO 999000.0f   // PM.cc:437 initial best_match_err = 1e6
@@ -516,7 +523,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     __shared__ float2 s_par2[K1_WARPS][32];  // per owner lane: epipolar-line angle, rotated orientation
     __shared__ uint32_t s_beste[K1_WARPS][32];
     __shared__ uint32_t s_bestu[K1_WARPS][32];
-    __shared__ uint32_t s_tie[K1_WARPS];
+    __shared__ uint32_t s_tie[K1_WARPS][32];  // per owner lane: two best errs too close for the float shortcut
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -528,17 +535,24 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     uint32_t* bestu = s_bestu[wib];
     float4* par4 = s_par4[wib];
     float2* par2 = s_par2[wib];
+    uint32_t* tie = s_tie[wib];
     const float colsf = (float)A.W;
     const float inv_theta_f = (float)A.inv_THETA;
     const size_t arc_plane = (size_t)A.H * A.arc_pitch;
 
-  // persistent warps: the grid is sized to the machine, every warp draws 32-entry tasks until none are left
+  // persistent warps: the grid is sized to the machine; every warp draws (32 list entries x 1 neighbour)
+  // tasks until none are left.  Tasks are neighbour-major, so at any time the resident warps read the
+  // planes of one or two neighbour key frames (L2-resident), and a task is short enough (~1/10 of a
+  // pixel's work) that the last warps to finish do not leave the machine idle for long.
+  const unsigned nblk = ((unsigned)count + 31u) >> 5;
+  const unsigned long long ntask = (unsigned long long)nblk * (unsigned)A.n;
   for (;;) {
     unsigned task = 0;
     if (lane == 0) task = atomicAdd(A.task_counter, 1u);
     task = __shfl_sync(full, task, 0);
-    if ((long long)task * 32 >= (long long)count) break;
-    const int entry = (int)task * 32 + lane;
+    if ((unsigned long long)task >= ntask) break;
+    const int j = (int)(task / nblk);
+    const int entry = (int)(task - (unsigned)j * nblk) * 32 + lane;
     const bool valid = entry < count;
 
     int x = 0, y = 0;
@@ -554,7 +568,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     const float xp0 = (xf - A.cx) / A.fx, xp1 = (yf - A.cy) / A.fy;                   // PM.cc:893, 862
     const double xp0d = (double)xp0, xp1d = (double)xp1;
 
-    for (int j = 0; j < A.n; ++j) {
+    {
         const NbrConst& N = A.nb[j];
         // ---------------- (A) line, slope test, search range: PM.cc:389-393, 877-910 ----------------
         const float a = xf * N.F[0] + yf * N.F[3] + N.F[6];
@@ -610,7 +624,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         par4[lane] = make_float4(ab, cb, I1, g1);
         par2[lane] = make_float2(th_epi, apr);
         beste[lane] = 0x7f800000u;  // +inf
-        if (lane == 0) s_tie[wib] = 0;
+        tie[lane] = 0;
         __syncwarp();
 
         // ---------------- (C) evaluate queued candidates, one per lane ----------------
@@ -657,11 +671,11 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                                 const uint32_t old = atomicMin(&beste[owner], eb);
                                 const float fo = __uint_as_float(old);
                                 const float lo = fminf(ef, fo), hi = fmaxf(ef, fo);
-                                if (hi - lo <= __fmaf_rn(lo, K1_TIE_REL, 1e-30f)) atomicOr(&s_tie[wib], 1u << owner);
+                                if (hi - lo <= __fmaf_rn(lo, K1_TIE_REL, 1e-30f)) tie[owner] = 1u;  // benign race: every writer stores 1
                                 won = eb < old;
                             }
                         } else {  // never with u8 images (err <= ~2.1e5); keep the 1e6 limit exact anyway
-                            atomicOr(&s_tie[wib], 1u << owner);
+                            tie[owner] = 1u;
                         }
                     }
                 }
@@ -681,15 +695,38 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                 const int v = __shfl_up_sync(full, incl, dlt);
                 if (lane >= dlt) incl += v;
             }
-            int pos = qn + incl - cnt;
+            const int total = __shfl_sync(full, incl, 31);
             const uint32_t tag = ((uint32_t)lane << 16) | (uint32_t)col_base;
-            while (m) {
-                const int bit = __ffs((int)m) - 1;
-                m &= m - 1;
-                queue[pos++] = tag + (uint32_t)bit;
+            int pos = qn + incl - cnt;
+            if (total <= K1_QHALF) {
+                while (m) {
+                    const int bit = __ffs((int)m) - 1;
+                    m &= m - 1;
+                    queue[pos++] = tag + (uint32_t)bit;
+                }
+                qn += total;
+                __syncwarp();
+            } else {  // rare: more than the queue holds at once -- lanes 0..15, evaluate, then lanes 16..31
+                const int half = __shfl_sync(full, incl, 15);
+                if (lane < 16)
+                    while (m) {
+                        const int bit = __ffs((int)m) - 1;
+                        m &= m - 1;
+                        queue[pos++] = tag + (uint32_t)bit;
+                    }
+                qn += half;
+                __syncwarp();
+                drain(false);
+                pos = qn + incl - cnt - half;
+                if (lane >= 16)
+                    while (m) {
+                        const int bit = __ffs((int)m) - 1;
+                        m &= m - 1;
+                        queue[pos++] = tag + (uint32_t)bit;
+                    }
+                qn += total - half;
+                __syncwarp();
             }
-            qn += __shfl_sync(full, incl, 31);
-            __syncwarp();
         };
 
         const int u_end = min(u_hi, A.W - 1);
@@ -731,7 +768,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
 
         // ---------------- (D) refinement + hypothesis: PM.cc:446-463, 806-829 ----------------
         int bj = -1;
-        if ((s_tie[wib] >> lane) & 1u) {
+        if (tie[lane]) {
             LineScan L;
             L.ab = ab; L.cb = cb; L.I1 = I1; L.g1 = g1; L.th_epi = th_epi; L.apr = apr; L.u_lo = u_lo; L.u_hi = u_hi;
             bj = exact_line_scan(A, N, L);
@@ -796,7 +833,7 @@ struct FuseArgs {
 };
 
 template <int NT>
-__global__ void __launch_bounds__(128) k1_fuse(const FuseArgs F) {
+__global__ void __launch_bounds__(128, K1F_MIN_BLOCKS) k1_fuse(const FuseArgs F) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= F.meta->active_count) return;
     float hd[NT], hs[NT];
@@ -1070,7 +1107,46 @@ __global__ void __launch_bounds__(256) k_build_vlist(const float* __restrict__ d
 //    from a float estimate (relative error < 4e-7) unless it lies within 1e-5 of the threshold or an
 //    operand is tiny; then the double expression itself is evaluated.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k4_inter_check(const __grid_constant__ InterArgs A) {
+struct K4Proj {  // projection of one pixel into one neighbour + the four depth taps, PM.cc:675-705
+    bool inb;
+    float rz, depthj;
+    const float* spl;
+    float d[4];
+};
+
+__device__ __forceinline__ void k4_project(const InterArgs& A, const InterNbr& N, float xp0, float xp1, double xp0d, double xp1d,
+                                           float depthp, double inv_dp, K4Proj& P) {
+    // temp = gemm(Rji, xp, 1/depthp, tji, 1); Xj = K*temp (small path, float left to right)
+    const float q0 = N.R[0] * xp0 + N.R[1] * xp1 + N.R[2] * 1.0f;
+    const float q1 = N.R[3] * xp0 + N.R[4] * xp1 + N.R[5] * 1.0f;
+    const float q2 = N.R[6] * xp0 + N.R[7] * xp1 + N.R[8] * 1.0f;
+    const float t0 = (float)__fma_rn((double)q0, inv_dp, N.td[0]);
+    const float t1 = (float)__fma_rn((double)q1, inv_dp, N.td[1]);
+    const float t2 = (float)__fma_rn((double)q2, inv_dp, N.td[2]);
+    const float X0 = N.fx * t0 + 0.0f * t1 + N.cx * t2;
+    const float X1 = 0.0f * t0 + N.fy * t1 + N.cy * t2;
+    const float X2 = 0.0f * t0 + 0.0f * t1 + 1.0f * t2;
+    const float inv = 1.0f / X2;  // Xj/Xj(2): convertTo with alpha = 1./s
+    const float xj = X0 * inv, yj = X1 * inv;
+    P.inb = xj >= 0 && xj < (float)(A.W - 1) && yj >= 0 && yj < (float)(A.H - 1);  // PM.cc:695
+    // Eq. 12, PM.cc:684-688
+    P.rz = (float)(N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d));
+    P.depthj = depthp / (P.rz + depthp * N.t[2]);
+    P.spl = N.sigma;
+    P.d[0] = P.d[1] = P.d[2] = P.d[3] = 0.f;
+    if (P.inb) {
+        const int x0 = (int)xj, y0 = (int)yj;  // floor of a non-negative float
+        const size_t q = (size_t)y0 * A.pitch_f + x0;
+        const float* dpl = N.depth + q;
+        P.spl = N.sigma + q;
+        P.d[0] = __ldg(dpl);                  // taps (y0,x0) (y1,x0) (y0,x1) (y1,x1), PM.cc:705-752
+        P.d[1] = __ldg(dpl + A.pitch_f);
+        P.d[2] = __ldg(dpl + 1);
+        P.d[3] = __ldg(dpl + A.pitch_f + 1);
+    }
+}
+
+__global__ void __launch_bounds__(128, K4_MIN_BLOCKS) k4_inter_check(const __grid_constant__ InterArgs A) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= *A.vcount) return;
     const uint32_t ent = A.vlist[e];
@@ -1085,57 +1161,44 @@ __global__ void __launch_bounds__(128) k4_inter_check(const __grid_constant__ In
     const float thr = A.chi_inter, thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
     int nkf = 0;
     double sJr = 0.0, sJJ = 0.0;
+    // the projection and the depth taps of neighbour j+1 are issued before neighbour j is evaluated
+    K4Proj cur, nxt;
+    k4_project(A, A.nb[0], xp0, xp1, xp0d, xp1d, depthp, inv_dp, cur);
     for (int j = 0; j < A.n; ++j) {
-        const InterNbr& N = A.nb[j];
-        // temp = gemm(Rji, xp, 1/depthp, tji, 1); Xj = K*temp (small path, float left to right)
-        const float q0 = N.R[0] * xp0 + N.R[1] * xp1 + N.R[2] * 1.0f;
-        const float q1 = N.R[3] * xp0 + N.R[4] * xp1 + N.R[5] * 1.0f;
-        const float q2 = N.R[6] * xp0 + N.R[7] * xp1 + N.R[8] * 1.0f;
-        const float t0 = (float)__fma_rn((double)q0, inv_dp, N.td[0]);
-        const float t1 = (float)__fma_rn((double)q1, inv_dp, N.td[1]);
-        const float t2 = (float)__fma_rn((double)q2, inv_dp, N.td[2]);
-        const float X0 = N.fx * t0 + 0.0f * t1 + N.cx * t2;
-        const float X1 = 0.0f * t0 + N.fy * t1 + N.cy * t2;
-        const float X2 = 0.0f * t0 + 0.0f * t1 + 1.0f * t2;
-        const float inv = 1.0f / X2;  // Xj/Xj(2): convertTo with alpha = 1./s
-        const float xj = X0 * inv, yj = X1 * inv;
-        if (!(xj >= 0 && xj < (float)(A.W - 1) && yj >= 0 && yj < (float)(A.H - 1))) continue;  // PM.cc:695
-        // Eq. 12, PM.cc:684-688
-        const float rz = (float)(N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d));
-        const float depthj = depthp / (rz + depthp * N.t[2]);
-        const int x0 = (int)xj, y0 = (int)yj;  // floor of a non-negative float
-        const float* dpl = N.depth + (size_t)y0 * A.pitch_f + x0;
-        const float* spl = N.sigma + (size_t)y0 * A.pitch_f + x0;
-        const float d00 = __ldg(dpl), d10 = __ldg(dpl + A.pitch_f), d01 = __ldg(dpl + 1), d11 = __ldg(dpl + A.pitch_f + 1);
-        int ncomp = 0;
+        const float t2j = A.nb[j].t[2];
+        if (j + 1 < A.n) k4_project(A, A.nb[j + 1], xp0, xp1, xp0d, xp1d, depthp, inv_dp, nxt);
+        if (cur.inb) {
+            int ncomp = 0;
 #pragma unroll
-        for (int t = 0; t < 4; ++t) {  // taps (y0,x0) (y1,x0) (y0,x1) (y1,x1), PM.cc:705-752
-            const float d = t == 0 ? d00 : (t == 1 ? d10 : (t == 2 ? d01 : d11));
-            if (d > SD_EPS_F) {
-                const float s = __ldg(spl + (t & 1) * A.pitch_f + (t >> 1));
-                const float dl = depthj - d;
-                const float nf = dl * dl, qf = s * s;
-                const float est = __fdividef(nf, qf);
-                bool comp;
-                if (fminf(nf, qf) > 1e-30f && est < thr_lo) comp = true;
-                else if (fminf(nf, qf) > 1e-30f && est > thr_hi) comp = false;
-                else {
-                    const double dd = (double)dl;
-                    comp = (float)((dd * dd) / ((double)s * (double)s)) < thr;
-                }
-                if (comp) {
-                    ++ncomp;
-                    // Gauss-Newton terms, PM.cc:777-783 (order: neighbour j, then tap n)
-                    const float djn = 1 / d;
-                    const float d2sigma = djn * djn * s;
-                    const float Jn = -rz / d2sigma;
-                    const float rn = (djn - dp * rz - N.t[2]) / d2sigma;
-                    sJr = __fma_rn((double)Jn, (double)rn, sJr);
-                    sJJ = __fma_rn((double)Jn, (double)Jn, sJJ);
+            for (int t = 0; t < 4; ++t) {
+                const float d = cur.d[t];
+                if (d > SD_EPS_F) {
+                    const float s = __ldg(cur.spl + (t & 1) * A.pitch_f + (t >> 1));
+                    const float dl = cur.depthj - d;
+                    const float nf = dl * dl, qf = s * s;
+                    const float est = __fdividef(nf, qf);
+                    bool comp;
+                    if (fminf(nf, qf) > 1e-30f && est < thr_lo) comp = true;
+                    else if (fminf(nf, qf) > 1e-30f && est > thr_hi) comp = false;
+                    else {
+                        const double dd = (double)dl;
+                        comp = (float)((dd * dd) / ((double)s * (double)s)) < thr;
+                    }
+                    if (comp) {
+                        ++ncomp;
+                        // Gauss-Newton terms, PM.cc:777-783 (order: neighbour j, then tap n)
+                        const float djn = 1 / d;
+                        const float d2sigma = djn * djn * s;
+                        const float Jn = -cur.rz / d2sigma;
+                        const float rn = (djn - dp * cur.rz - t2j) / d2sigma;
+                        sJr = __fma_rn((double)Jn, (double)rn, sJr);
+                        sJJ = __fma_rn((double)Jn, (double)Jn, sJJ);
+                    }
                 }
             }
+            if (ncomp >= 1) ++nkf;
         }
-        if (ncomp >= 1) ++nkf;
+        cur = nxt;
     }
     float out;
     if (nkf < A.lambdaN) {

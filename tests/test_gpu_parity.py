@@ -339,3 +339,21 @@ def test_error_codes(pkg, synth, pipeline):
     assert e.value.code == -2
     assert ctx.launch_count() >= 4
     ctx.close()
+
+
+def test_dense_candidates_split_queue(pkg, po, synth, pipeline):
+    """Images whose every pixel passes the gradient and orientation gates (a sawtooth ramp): the arc-plane
+    words are full, one scan step queues more candidates than the per-warp queue holds and
+    k1_search takes the two-halves path; near-equal errs along the ramp also exercise the exact re-scan."""
+    scene = synth.Scene(SMALL_CAM, seed=3)
+    nkf, n = 7, 6
+    plan = pipeline.SequencePlan(scene, nkf, n)
+    yy, xx = np.mgrid[0:scene.h, 0:scene.w]
+    rng = np.random.default_rng(11)
+    images = {k: (((xx + 3 * k) * 9 + yy * 4) % 230 + rng.integers(0, 3, xx.shape)).astype(np.uint8) for k in plan.ids}
+    ora = run_oracle(po, plan, images)
+    ctx = run_gpu(pkg, pipeline, plan, images)
+    assert ctx.active_count(plan.ids[3]) > 0.9 * (scene.w - 4) * (scene.h - 4)
+    stats = assert_sequence_parity(po, ctx, ora, plan)
+    assert sum(s[0] for s in stats.values()) == 0 and sum(s[2] for s in stats.values()) == 0, stats
+    ctx.close()
