@@ -1,0 +1,104 @@
+"""One rank of the key-frame-sharded path, used by tests/test_gpu_sharded.py and by
+tools/gpu_shard_nccl.sh.  Launched once per rank with RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT set.
+
+  SHARD_BACKEND=nccl : one GPU per rank, the (inverse depth, sigma) halo maps travel GPU->GPU over NCCL
+  SHARD_BACKEND=gloo : every rank on cuda:0 (a single-GPU box), the same maps are staged through host
+                       memory and travel over gloo -- same sharding plan, same sd_export_maps /
+                       sd_import_maps calls, same kernels
+
+Every rank checks the key frames it owns against the CPU oracle run on the WHOLE sequence: sharding
+must not change a single value.  Exit code 0 = parity."""
+import importlib
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from __graft_entry__ import PKG_NAME, load_package  # noqa: E402
+
+
+def main():
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    backend = os.environ.get("SHARD_BACKEND", "gloo")
+    cam = os.environ.get("SHARD_CAM", "small")
+    nkf, n = int(os.environ.get("SHARD_NKF", "14")), int(os.environ.get("SHARD_NBR", "6"))
+    pkg = load_package()
+    synth = importlib.import_module(PKG_NAME + ".synth")
+    pipeline = importlib.import_module(PKG_NAME + ".pipeline")
+    sharding = importlib.import_module(PKG_NAME + ".sharding")
+    from oracle import pm_oracle as po
+
+    local = rank if backend == "nccl" else 0
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group(backend, rank=rank, world_size=world)
+
+    small = dict(w=320, h=240, fx=262.5, fy=262.5, cx=159.5, cy=119.5)
+    scene = synth.Scene(small if cam == "small" else cam, seed=77)
+    H, W = scene.h, scene.w
+    plan = pipeline.SequencePlan(scene, nkf, n)          # the whole sequence (host-side inputs are cheap)
+    shard = sharding.make_plan(nkf, world, rank, lambda k: plan.nbrs[k])
+    images = {k: scene.render(k) for k in plan.ids}
+
+    ctx = pkg.Context(local)
+    for k in shard.resident:                              # owned + image halo: K0 is recomputed locally
+        ctx.upload_keyframe(k, images[k], scene.K, plan.poses[k])
+    for k in shard.owned:
+        ctx.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
+
+    ext = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
+
+    def pack(ids):
+        t = torch.empty((len(ids), 2, H, W), dtype=torch.float32, device=dev)
+        with torch.cuda.stream(ext):
+            for i, k in enumerate(ids):
+                ctx.export_maps(k, t[i, 0].data_ptr(), t[i, 1].data_ptr())
+        ctx.sync()
+        return t if backend == "nccl" else t.cpu()
+
+    def alloc(cnt):
+        return torch.empty((cnt, 2, H, W), dtype=torch.float32, device=dev if backend == "nccl" else "cpu")
+
+    keep = []
+
+    def unpack(ids, t):
+        t = t.to(dev)
+        keep.append(t)
+        for i, k in enumerate(ids):
+            ctx.import_maps(k, t[i, 0].data_ptr(), t[i, 1].data_ptr())
+
+    with torch.cuda.stream(ext):                          # NCCL orders against the context's compute stream
+        nbytes = sharding.exchange_maps(shard, dist, pack, alloc, unpack)
+    for k in shard.owned:
+        ctx.interkf_check(k, plan.nbrs[k])
+        ctx.update_pointset(k)
+    ctx.sync()
+
+    ora = po.Oracle(threads=max(1, po.lib().ora_max_threads() // world))
+    for k in plan.ids:
+        ora.add_keyframe(k, images[k], scene.K, plan.poses[k])
+    for k in plan.ids:
+        ora.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
+    bad = 0
+    for k in shard.owned:
+        ora.interkf(k, plan.nbrs[k])
+        ora.pointset(k)
+        for which in (po.DEPTH, po.SIGMA, po.DEPTH_CHECKED, po.POINTS):
+            if not np.array_equal(ctx.plane(k, which), ora.plane(k, which)):
+                bad += 1
+                print(f"rank {rank}: key frame {k} plane {which} differs", flush=True)
+    valid = sum(int((ctx.plane(k, po.DEPTH_CHECKED) > 1e-6).sum()) for k in shard.owned)
+    print(f"rank {rank}/{world} [{backend}]: owned {shard.owned[0]}..{shard.owned[-1]}, image halo {shard.image_halo}, "
+          f"exchanged {nbytes / 1e6:.1f} MB, valid px {valid}, mismatching planes {bad}", flush=True)
+    ctx.close()
+    dist.barrier()
+    dist.destroy_process_group()
+    sys.exit(1 if bad or valid == 0 else 0)
+
+
+if __name__ == "__main__":
+    main()
