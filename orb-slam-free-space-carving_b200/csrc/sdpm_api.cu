@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <unordered_map>
@@ -53,13 +54,19 @@ struct sd_ctx {
     int device = 0;
     SdParams P;
     int W = 0, H = 0, pitch_f = 0, pitch_u8 = 0, arc_pitch = 0;
-    cudaStream_t s_up = nullptr, s_main = nullptr, s_dn = nullptr;
+    // s_up: upload + K0; s_srch: k1_search (low priority, fills the machine); s_main: everything after the
+    // search (k1_fuse .. K5, NCCL ordering) at high priority, so the short latency-bound kernels of key frame
+    // k run in the issue slots the search of key frame k+1 leaves idle; s_dn: downloads
+    cudaStream_t s_up = nullptr, s_srch = nullptr, s_main = nullptr, s_dn = nullptr;
     cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
     float *tmp_depth = nullptr, *tmp_sigma = nullptr;  // k1_fuse output / k23_intra input
-    float2* hyp = nullptr;                             // hypothesis buffer of k1_search, [neighbour][hyp_stride]
-    int hyp_stride = 0, hyp_rows = 0;
+    float2* hyp[2] = {nullptr, nullptr};               // hypothesis buffers of k1_search, [neighbour][hyp_stride], double-buffered
+    int hyp_stride = 0, hyp_rows = 0, hyp_turn = 0;
+    cudaEvent_t ev_srch[2] = {nullptr, nullptr};       // k1_search into hyp[b] done (s_srch)
+    cudaEvent_t ev_hypfree[2] = {nullptr, nullptr};    // k1_fuse out of hyp[b] done (s_main)
+    bool hypfree_valid[2] = {false, false};
     std::string err;
     uint64_t launches = 0;
     bool timing = false;
@@ -215,6 +222,8 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         // planes are being replaced: wait for everything already queued that may still read them
         CU(c, cudaEventRecord(c->ev_tmp, c->s_main));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
+        CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));
+        CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
         CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
     } else {
@@ -302,8 +311,15 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
     }
     c->chi_fuse_f = geom::round_up_to_float(c->P.chi2_fuse);
     c->chi_inter_f = geom::round_up_to_float(c->P.chi2_inter);
+    int prio_least = 0, prio_greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest);
     if (cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->s_main, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_greatest) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&c->s_srch, cudaStreamNonBlocking, prio_least) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_srch[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_srch[1], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_hypfree[0], cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&c->ev_hypfree[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->s_dn, cudaStreamNonBlocking) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_tmp, cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreate(&c->ev_span_a) != cudaSuccess || cudaEventCreate(&c->ev_span_b) != cudaSuccess) {
@@ -325,7 +341,10 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
             return SD_ERR_CUDA;
         }
         c->sm_count = prop.multiProcessorCount;
-        c->k1_grid = c->sm_count * per_sm;
+        // SDPM_K1_BLOCKS_PER_SM < occupancy leaves room for the post-search kernels of the previous key frame
+        int use = per_sm;
+        if (const char* e = getenv("SDPM_K1_BLOCKS_PER_SM")) use = std::max(1, std::min(per_sm, atoi(e)));
+        c->k1_grid = c->sm_count * use;
     }
     *out = c;
     return SD_OK;
@@ -341,12 +360,18 @@ int sd_destroy(sd_ctx* c) {
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     cudaFree(c->tmp_depth);
     cudaFree(c->tmp_sigma);
-    cudaFree(c->hyp);
+    cudaFree(c->hyp[0]);
+    cudaFree(c->hyp[1]);
+    for (int b = 0; b < 2; ++b) {
+        if (c->ev_srch[b]) cudaEventDestroy(c->ev_srch[b]);
+        if (c->ev_hypfree[b]) cudaEventDestroy(c->ev_hypfree[b]);
+    }
     if (c->ev_tmp) cudaEventDestroy(c->ev_tmp);
     if (c->ev_span_a) cudaEventDestroy(c->ev_span_a);
     if (c->ev_span_b) cudaEventDestroy(c->ev_span_b);
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_main);
+    cudaStreamDestroy(c->s_srch);
     cudaStreamDestroy(c->s_dn);
     delete c;
     return SD_OK;
@@ -393,49 +418,62 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     A.maxd = max_invdepth;
     A.mind_d = (double)min_invdepth;
     A.maxd_d = (double)max_invdepth;
-    if (c->hyp_rows < n) {  // grow-only scratch: n x (W*H) hypotheses
+    if (c->hyp_rows < n) {  // grow-only scratch: 2 x n x (W*H) hypotheses
+        CU(c, cudaStreamSynchronize(c->s_srch));
         CU(c, cudaStreamSynchronize(c->s_main));
-        cudaFree(c->hyp);
-        c->hyp = nullptr;
+        for (int b = 0; b < 2; ++b) {
+            cudaFree(c->hyp[b]);
+            c->hyp[b] = nullptr;
+            c->hypfree_valid[b] = false;
+        }
         c->hyp_rows = 0;
         c->hyp_stride = (int)align_up((size_t)c->W * c->H, 64);
-        CU(c, cudaMalloc(&c->hyp, (size_t)n * c->hyp_stride * sizeof(float2)));
+        for (int b = 0; b < 2; ++b) CU(c, cudaMalloc(&c->hyp[b], (size_t)n * c->hyp_stride * sizeof(float2)));
         c->hyp_rows = n;
     }
-    A.hyp = c->hyp;
+    const int hb = c->hyp_turn;
+    c->hyp_turn ^= 1;
+    A.hyp = c->hyp[hb];
     A.hyp_stride = c->hyp_stride;
-    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
+    // ---- search stream: k1_search of this key frame into hyp[hb] ----
+    CU(c, cudaStreamWaitEvent(c->s_srch, s->ev_up, 0));
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
         if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
         fill_nbr(s, nb, nbr_rot_deg ? nbr_rot_deg[j] : 0.f, A.nb[j]);
-        CU(c, cudaStreamWaitEvent(c->s_main, nb->ev_up, 0));
+        CU(c, cudaStreamWaitEvent(c->s_srch, nb->ev_up, 0));
     }
+    if (c->hypfree_valid[hb]) CU(c, cudaStreamWaitEvent(c->s_srch, c->ev_hypfree[hb], 0));
+    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), c->s_srch));
+    {
+        ScopedTimer t(c, c->s_srch, T_SEARCH);
+        k1_search<<<c->k1_grid, K1_WARPS * 32, 0, c->s_srch>>>(A);
+    }
+    CU(c, cudaEventRecord(c->ev_srch[hb], c->s_srch));
+    // ---- main stream: fusion into the scratch planes (zero = no depth), then k23_intra reads them with a
+    // halo and writes the key frame's own planes ----
+    CU(c, cudaStreamWaitEvent(c->s_main, c->ev_srch[hb], 0));
     if (s->dn_pending) {  // a download of the old maps may still be in flight
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
     }
-    // k1_search scatters its results into the context's scratch planes (zero = no depth); k23_intra
-    // reads them with a halo and writes the key frame's own planes
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
     CU(c, cudaMemsetAsync(c->tmp_depth, 0, fplane, c->s_main));
     CU(c, cudaMemsetAsync(c->tmp_sigma, 0, fplane, c->s_main));
-    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int) + sizeof(int), c->s_main));  // + valid_count
-    {
-        ScopedTimer t(c, c->s_main, T_SEARCH);
-        k1_search<<<c->k1_grid, K1_WARPS * 32, 0, c->s_main>>>(A);
-    }
+    CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_main));
     {
         ScopedTimer t(c, c->s_main, T_FUSE);
         FuseArgs F;
         F.n = n; F.lambdaN = c->P.lambdaN; F.pitch_f = c->pitch_f; F.hyp_stride = c->hyp_stride; F.chi_fuse = c->chi_fuse_f;
-        F.hyp = c->hyp; F.list = s->list; F.meta = s->meta; F.depth = c->tmp_depth; F.sigma = c->tmp_sigma;
+        F.hyp = c->hyp[hb]; F.list = s->list; F.meta = s->meta; F.depth = c->tmp_depth; F.sigma = c->tmp_sigma;
         const int blocks = ((c->W - 2 * c->P.border) * (c->H - 2 * c->P.border) + 127) / 128;  // the list's capacity
         if (n <= 6) k1_fuse<6><<<blocks, 128, 0, c->s_main>>>(F);
         else if (n <= 10) k1_fuse<10><<<blocks, 128, 0, c->s_main>>>(F);
         else if (n <= 16) k1_fuse<16><<<blocks, 128, 0, c->s_main>>>(F);
         else k1_fuse<SD_MAX_NEIGHBOURS><<<blocks, 128, 0, c->s_main>>>(F);
     }
+    CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
+    c->hypfree_valid[hb] = true;
     {
         ScopedTimer t(c, c->s_main, T_INTRA);
         IntraArgs S;
@@ -651,6 +689,7 @@ int sd_sync(sd_ctx* c) {
     if (!c) return SD_ERR_INVALID_ARG;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaStreamSynchronize(c->s_up));
+    CU(c, cudaStreamSynchronize(c->s_srch));
     CU(c, cudaStreamSynchronize(c->s_main));
     CU(c, cudaStreamSynchronize(c->s_dn));
     for (auto& kv : c->kfs) kv.second->dn_pending = false;
@@ -678,6 +717,7 @@ int sd_span_begin(sd_ctx* c) {
     CU(c, cudaEventRecord(c->ev_span_a, c->s_main));
     // later work on the other two streams must not start before the span does
     CU(c, cudaStreamWaitEvent(c->s_up, c->ev_span_a, 0));
+    CU(c, cudaStreamWaitEvent(c->s_srch, c->ev_span_a, 0));
     CU(c, cudaStreamWaitEvent(c->s_dn, c->ev_span_a, 0));
     return SD_OK;
 }
@@ -686,6 +726,8 @@ int sd_span_end(sd_ctx* c, double* ms) {
     if (!c || !ms) return SD_ERR_INVALID_ARG;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaEventRecord(c->ev_tmp, c->s_up));
+    CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
+    CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
     CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
