@@ -41,6 +41,10 @@ struct Slot {
     cudaEvent_t ev_up = nullptr;  // upload + K0 done (s_up)
     cudaEvent_t ev_dn = nullptr;  // last download issued (s_dn)
     bool dn_pending = false;
+    cudaEvent_t ev_sd = nullptr;   // (depth, sigma) maps ready: after k23_intra / sd_import_maps (s_main)
+    cudaEvent_t ev_chk = nullptr;  // last K4 / K5 of this key frame (s_chk)
+    bool sd_recorded = false, chk_recorded = false;
+    long long rd_idx = -1;         // ring index of the last K4 that read this key frame's maps (own or as a neighbour)
 };
 
 struct TimedSpan {
@@ -57,7 +61,12 @@ struct sd_ctx {
     // s_up: upload + K0; s_srch: k1_search (low priority, fills the machine); s_main: everything after the
     // search (k1_fuse .. K5, NCCL ordering) at high priority, so the short latency-bound kernels of key frame
     // k run in the issue slots the search of key frame k+1 leaves idle; s_dn: downloads
-    cudaStream_t s_up = nullptr, s_srch = nullptr, s_main = nullptr, s_dn = nullptr;
+    // s_chk: K4 + K5 (high priority), ordered against s_main by per-key-frame events, so the inter-key-frame
+    // check of key frame j overlaps the fusion / intra stage of a later one
+    cudaStream_t s_up = nullptr, s_srch = nullptr, s_main = nullptr, s_chk = nullptr, s_dn = nullptr;
+    static const int RING = 64;
+    cudaEvent_t ev_ring[RING] = {nullptr};  // ev_ring[i % RING]: K4 number i done (s_chk)
+    long long ring_i = 0;
     cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
@@ -133,6 +142,8 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->meta = (KfMeta*)p;
     cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_dn, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&s->ev_sd, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&s->ev_chk, cudaEventDisableTiming);
     *out = s;
     return SD_OK;
 }
@@ -143,6 +154,8 @@ void free_slot(Slot* s) {
     cudaFree(s->points);
     if (s->ev_up) cudaEventDestroy(s->ev_up);
     if (s->ev_dn) cudaEventDestroy(s->ev_dn);
+    if (s->ev_sd) cudaEventDestroy(s->ev_sd);
+    if (s->ev_chk) cudaEventDestroy(s->ev_chk);
     delete s;
 }
 
@@ -224,6 +237,8 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
         CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
+        CU(c, cudaEventRecord(c->ev_tmp, c->s_chk));
+        CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
         CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
     } else {
@@ -234,6 +249,8 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
     }
     s->has_semidense = s->has_checked = s->has_points = s->pose_changed = s->vlist_ok = false;
     s->dn_pending = false;
+    s->sd_recorded = s->chk_recorded = false;
+    s->rd_idx = -1;
     std::memcpy(s->K, K, sizeof(s->K));
     set_pose_fields(s, Tcw);
 
@@ -250,6 +267,16 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_up, c->s_up));
     return SD_OK;
+}
+
+// Before `stream` overwrites the maps of a key frame: wait for the K4 / K5 launches (s_chk) that read them.
+// ev_ring slots are reused by later K4 launches of the same stream, so a recycled event still implies the
+// one it replaced.
+cudaError_t wait_map_readers(sd_ctx* c, Slot* s, cudaStream_t stream) {
+    cudaError_t e = cudaSuccess;
+    if (s->rd_idx >= 0) e = cudaStreamWaitEvent(stream, c->ev_ring[s->rd_idx % sd_ctx::RING], 0);
+    if (e == cudaSuccess && s->chk_recorded) e = cudaStreamWaitEvent(stream, s->ev_chk, 0);
+    return e;
 }
 
 void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
@@ -316,6 +343,7 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
     if (cudaStreamCreateWithFlags(&c->s_up, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithPriority(&c->s_main, cudaStreamNonBlocking, prio_greatest) != cudaSuccess ||
         cudaStreamCreateWithPriority(&c->s_srch, cudaStreamNonBlocking, prio_least) != cudaSuccess ||
+        cudaStreamCreateWithPriority(&c->s_chk, cudaStreamNonBlocking, prio_greatest) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_srch[0], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_srch[1], cudaEventDisableTiming) != cudaSuccess ||
         cudaEventCreateWithFlags(&c->ev_hypfree[0], cudaEventDisableTiming) != cudaSuccess ||
@@ -345,6 +373,11 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
         int use = per_sm;
         if (const char* e = getenv("SDPM_K1_BLOCKS_PER_SM")) use = std::max(1, std::min(per_sm, atoi(e)));
         c->k1_grid = c->sm_count * use;
+        for (int i = 0; i < sd_ctx::RING; ++i)
+            if (cudaEventCreateWithFlags(&c->ev_ring[i], cudaEventDisableTiming) != cudaSuccess) {
+                delete c;
+                return SD_ERR_CUDA;
+            }
     }
     *out = c;
     return SD_OK;
@@ -372,6 +405,9 @@ int sd_destroy(sd_ctx* c) {
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_main);
     cudaStreamDestroy(c->s_srch);
+    cudaStreamDestroy(c->s_chk);
+    for (int i = 0; i < sd_ctx::RING; ++i)
+        if (c->ev_ring[i]) cudaEventDestroy(c->ev_ring[i]);
     cudaStreamDestroy(c->s_dn);
     delete c;
     return SD_OK;
@@ -457,6 +493,7 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
     }
+    CU(c, wait_map_readers(c, s, c->s_main));  // k23_intra below overwrites this key frame's maps and list
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
     CU(c, cudaMemsetAsync(c->tmp_depth, 0, fplane, c->s_main));
     CU(c, cudaMemsetAsync(c->tmp_sigma, 0, fplane, c->s_main));
@@ -486,6 +523,8 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         k23_intra<true, true><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
     }
     CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(s->ev_sd, c->s_main));
+    s->sd_recorded = true;
     s->has_semidense = true;
     s->vlist_ok = true;
     s->has_checked = false;
@@ -517,29 +556,39 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
         N.fx = nb->K[0]; N.fy = nb->K[1]; N.cx = nb->K[2]; N.cy = nb->K[3];
         N.depth = nb->depth;
         N.sigma = nb->sigma;
+        if (nb->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, nb->ev_sd, 0));
     }
+    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_sd, 0));
     if (s->dn_pending) {
-        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_dn, 0));
         s->dn_pending = false;
     }
     if (!s->vlist_ok) {  // maps installed by sd_import_maps: rebuild the list and the plane k4 patches
         const size_t pb = (size_t)c->pitch_f * sizeof(float);
-        CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_main));
-        CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_main));
+        CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_chk));
+        CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_chk));
         dim3 grd((c->W + 31) / 32, (c->H + 7) / 8);
-        k_build_vlist<<<grd, 256, 0, c->s_main>>>(s->depth, c->pitch_f, c->W, c->H, s->vlist, &s->meta->valid_count);
+        k_build_vlist<<<grd, 256, 0, c->s_chk>>>(s->depth, c->pitch_f, c->W, c->H, s->vlist, &s->meta->valid_count);
         c->launches++;
         s->vlist_ok = true;
     } else if (s->has_checked) {  // a repeated check starts again from the intra-KF map
         const size_t pb = (size_t)c->pitch_f * sizeof(float);
-        CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_main));
+        CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_chk));
     }
     {
-        ScopedTimer t(c, c->s_main, T_INTER);
+        ScopedTimer t(c, c->s_chk, T_INTER);
         const int worst = (c->W - 4) * (c->H - 4);  // the list holds pixels inside the 2-px frame only
-        k4_inter_check<<<(worst + 127) / 128, 128, 0, c->s_main>>>(A);
+        k4_inter_check<<<(worst + 127) / 128, 128, 0, c->s_chk>>>(A);
     }
     CU(c, cudaGetLastError());
+    {   // this launch read the maps of kf and of its neighbours: writers of those maps wait for it
+        const long long idx = c->ring_i++;
+        CU(c, cudaEventRecord(c->ev_ring[idx % sd_ctx::RING], c->s_chk));
+        s->rd_idx = idx;
+        for (int j = 0; j < n; ++j) find(c, nbr_ids[j])->rd_idx = idx;
+        CU(c, cudaEventRecord(s->ev_chk, c->s_chk));
+        s->chk_recorded = true;
+    }
     s->has_checked = true;
     s->has_points = false;
     return SD_OK;
@@ -552,8 +601,9 @@ int sd_update_pointset(sd_ctx* c, int kf_id) {
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     CU(c, cudaSetDevice(c->device));
     if (!s->points) CU(c, cudaMalloc(&s->points, (size_t)c->W * c->H * 3 * sizeof(float)));
+    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_sd, 0));
     if (s->dn_pending) {
-        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_dn, 0));
         s->dn_pending = false;
     }
     PointArgs A;
@@ -563,11 +613,13 @@ int sd_update_pointset(sd_ctx* c, int kf_id) {
     A.depth = s->has_checked ? s->depth_chk : s->depth;
     A.points = s->points;
     {
-        ScopedTimer t(c, c->s_main, T_POINTS);
+        ScopedTimer t(c, c->s_chk, T_POINTS);
         dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
-        k5_pointset<<<grd, blk, 0, c->s_main>>>(A);
+        k5_pointset<<<grd, blk, 0, c->s_chk>>>(A);
     }
     CU(c, cudaGetLastError());
+    CU(c, cudaEventRecord(s->ev_chk, c->s_chk));
+    s->chk_recorded = true;
     s->has_points = true;
     s->pose_changed = false;
     return SD_OK;
@@ -580,8 +632,8 @@ int sd_download_async(sd_ctx* c, int kf_id, float* depth, float* sigma, float* p
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     if (points && !s->has_points) return fail(c, SD_ERR_NOT_READY, "key frame %d has no point set", kf_id);
     CU(c, cudaSetDevice(c->device));
-    CU(c, cudaEventRecord(c->ev_tmp, c->s_main));
-    CU(c, cudaStreamWaitEvent(c->s_dn, c->ev_tmp, 0));
+    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_sd, 0));
+    if (s->chk_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_chk, 0));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
     if (depth) CU(c, cudaMemcpy2DAsync(depth, wb, s->has_checked ? s->depth_chk : s->depth, pb, wb, c->H, cudaMemcpyDeviceToHost, c->s_dn));
     if (sigma) CU(c, cudaMemcpy2DAsync(sigma, wb, s->sigma, pb, wb, c->H, cudaMemcpyDeviceToHost, c->s_dn));
@@ -616,6 +668,7 @@ int sd_download_plane(sd_ctx* c, int kf_id, int which, float* out) {
     if (!src) return fail(c, SD_ERR_NOT_READY, "plane %d of key frame %d not computed", which, kf_id);
     CU(c, cudaStreamSynchronize(c->s_up));
     CU(c, cudaStreamSynchronize(c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_chk));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
     if (which == 5) CU(c, cudaMemcpy(out, src, (size_t)c->W * c->H * 3 * sizeof(float), cudaMemcpyDeviceToHost));
     else CU(c, cudaMemcpy2D(out, wb, src, pb, wb, c->H, cudaMemcpyDeviceToHost));
@@ -665,8 +718,15 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
     CU(c, cudaSetDevice(c->device));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    CU(c, wait_map_readers(c, s, c->s_main));
+    if (s->dn_pending) {
+        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        s->dn_pending = false;
+    }
     CU(c, cudaMemcpy2DAsync(s->depth, pb, depth_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     CU(c, cudaMemcpy2DAsync(s->sigma, pb, sigma_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
+    CU(c, cudaEventRecord(s->ev_sd, c->s_main));
+    s->sd_recorded = true;
     s->has_semidense = true;
     s->has_checked = false;
     s->vlist_ok = false;
@@ -691,6 +751,7 @@ int sd_sync(sd_ctx* c) {
     CU(c, cudaStreamSynchronize(c->s_up));
     CU(c, cudaStreamSynchronize(c->s_srch));
     CU(c, cudaStreamSynchronize(c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_chk));
     CU(c, cudaStreamSynchronize(c->s_dn));
     for (auto& kv : c->kfs) kv.second->dn_pending = false;
     if (c->timing) collect_spans(c);
@@ -718,6 +779,7 @@ int sd_span_begin(sd_ctx* c) {
     // later work on the other two streams must not start before the span does
     CU(c, cudaStreamWaitEvent(c->s_up, c->ev_span_a, 0));
     CU(c, cudaStreamWaitEvent(c->s_srch, c->ev_span_a, 0));
+    CU(c, cudaStreamWaitEvent(c->s_chk, c->ev_span_a, 0));
     CU(c, cudaStreamWaitEvent(c->s_dn, c->ev_span_a, 0));
     return SD_OK;
 }
@@ -728,6 +790,8 @@ int sd_span_end(sd_ctx* c, double* ms) {
     CU(c, cudaEventRecord(c->ev_tmp, c->s_up));
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
     CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));
+    CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
+    CU(c, cudaEventRecord(c->ev_tmp, c->s_chk));
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
     CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
