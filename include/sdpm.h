@@ -100,6 +100,23 @@ int sd_interkf_check(sd_ctx* ctx, int kf_id, const int* nbr_ids, int n);
 /* UpdateSemiDensePointSet, PM.cc:337-367 (uses depth_checked when present, else depth). */
 int sd_update_pointset(sd_ctx* ctx, int kf_id);
 
+/* Confident semi-dense points of one key frame, compacted on the device: the feed for the CARV transcript
+ * (extra 3-D points per key frame enter the Delaunay carving through
+ * SFMTranscriptInterface_ORBSLAM::addKeyFrameInsertionWithLinesEntry, src/Modeler/SFMTranscriptInterface_ORBSLAM.cpp:319-374,
+ * called from src/Modeler/Modeler.cc:118-124) and for the .obj dump of PM.cc:100-132.
+ * Selection is the reference's own (PM.cc:120-121): skip if `sigma > max_sigma` (the float against a double, 0.01 there),
+ * keep if `depth > 0.000001`; whole image, raster order; depth = depth_checked when the inter-KF stage ran.
+ * If max_points > 0 and more pixels qualify, the max_points with the smallest sigma are kept (ties: first in raster order),
+ * still emitted in raster order.  xyz are world points with the arithmetic and the current pose of UpdateSemiDensePointSet
+ * (PM.cc:337-367); sd_update_pointset need not have run.  Host outputs hold `capacity` entries each (xyz 3 floats per
+ * entry; sigma and pixel = y << 16 | x may be NULL); *count is the number selected (copy stops at capacity).  Synchronises. */
+int sd_confident_points(sd_ctx* ctx, int kf_id, double max_sigma, int max_points, int capacity, float* xyz, float* sigma,
+                        uint32_t* pixel, int* count);
+/* Same, results left in device scratch owned by the context (valid until the next sd_confident_points* call on it);
+ * *confident (nullable) = pixels passing the predicate before the max_points cut. */
+int sd_confident_points_device(sd_ctx* ctx, int kf_id, double max_sigma, int max_points, const float** xyz_dev,
+                               const float** sigma_dev, const uint32_t** pixel_dev, int* count, int* confident);
+
 /* Copy results to host buffers (each may be NULL): depth = depth_checked when the inter-KF stage
  * ran, else the intra-KF map; W*H floats each, points H*3W floats.  Synchronises. */
 int sd_download(sd_ctx* ctx, int kf_id, float* depth, float* sigma, float* points);

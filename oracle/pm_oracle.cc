@@ -794,6 +794,59 @@ int ora_pointset(void* h, int kf_id) {
     return 0;
 }
 
+// The selection of the .obj dump, PM.cc:114-127 (whole image, raster order: skip if depth_sigma_ > 0.01,
+// keep if depth_map_ > 0.000001), with the threshold as a parameter, returned as a list -- the shape in which the
+// CARV transcript ingests extra points per key frame (SFMTranscriptInterface_ORBSLAM.cpp:319-374).
+// Build-defined extension (no counterpart in the reference): if max_points > 0 and more pixels qualify, the
+// max_points with the smallest sigma are kept (total order on the float bits, ties: raster order), in raster order.
+int ora_confident_points(void* h, int kf_id, double max_sigma, int max_points, int capacity, float* xyz, float* sigma, uint32_t* pixel) {
+    KeyFrame* kf = find((Oracle*)h, kf_id);
+    if (!kf || !kf->semidense_flag_) return -1;
+    UpdateSemiDensePointSet(*kf);  // current pose, current depth map (PM.cc:321-334 refreshes it the same way)
+    const int rows = kf->rows, cols = kf->cols;
+    const std::vector<float>& dm = kf->interKF_depth_flag_ ? kf->depth_checked_ : kf->depth_map_;
+    std::vector<uint32_t> sel;
+    for (int y = 0; y < rows; y++)
+        for (int x = 0; x < cols; x++) {
+            const size_t o = (size_t)y * cols + x;
+            if (kf->depth_sigma_[o] > max_sigma) continue;
+            if (dm[o] > 0.000001) sel.push_back((uint32_t)o);
+        }
+    if (max_points > 0 && (int)sel.size() > max_points) {
+        auto key = [&](uint32_t o) {
+            uint32_t b;
+            std::memcpy(&b, &kf->depth_sigma_[o], 4);
+            return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+        };
+        std::stable_sort(sel.begin(), sel.end(), [&](uint32_t a, uint32_t b) { return key(a) < key(b); });
+        sel.resize(max_points);
+        std::sort(sel.begin(), sel.end());
+    }
+    const int n = (int)sel.size();
+    for (int i = 0; i < n && i < capacity; ++i) {
+        const uint32_t o = sel[i];
+        const int y = (int)(o / cols), x = (int)(o % cols);
+        if (xyz) std::memcpy(xyz + 3 * (size_t)i, &kf->SemiDensePointSets_[(size_t)y * cols * 3 + 3 * x], 3 * sizeof(float));
+        if (sigma) sigma[i] = kf->depth_sigma_[o];
+        if (pixel) pixel[i] = ((uint32_t)y << 16) | (uint32_t)x;
+    }
+    return n;
+}
+
+// test hook: install caller-made (depth, sigma) maps as the intra-KF result of a key frame (the counterpart of
+// sd_import_maps), so crafted planes can be pushed through the later stages
+int ora_set_maps(void* h, int kf_id, const float* depth, const float* sigma) {
+    KeyFrame* kf = find((Oracle*)h, kf_id);
+    if (!kf) return -1;
+    const size_t n = (size_t)kf->rows * kf->cols;
+    kf->depth_map_.assign(depth, depth + n);
+    kf->depth_sigma_.assign(sigma, sigma + n);
+    kf->semidense_flag_ = true;
+    kf->interKF_depth_flag_ = false;
+    kf->depth_checked_.clear();
+    return 0;
+}
+
 int ora_get_plane(void* h, int kf_id, int what, float* out) {
     KeyFrame* kf = find((Oracle*)h, kf_id);
     if (!kf) return -1;

@@ -49,6 +49,12 @@ int ora_semidense(void* h, int kf_id, const int* nbr_ids, const float* nbr_rot_d
 int ora_interkf(void* h, int kf_id, const int* nbr_ids, int n);
 /* PM.cc:337-367 */
 int ora_pointset(void* h, int kf_id);
+/* PM.cc:114-127 selection (sigma > max_sigma: skip; depth > 1e-6: keep) as a point list, optional smallest-sigma cut;
+ * returns the number selected (outputs hold `capacity` entries, each nullable) */
+int ora_confident_points(void* h, int kf_id, double max_sigma, int max_points, int capacity, float* xyz, float* sigma, uint32_t* pixel);
+
+/* test hook: install (depth, sigma) maps as the intra-KF result of a key frame (counterpart of sd_import_maps) */
+int ora_set_maps(void* h, int kf_id, const float* depth, const float* sigma);
 
 enum { ORA_GRAD = 0, ORA_THETA = 1, ORA_DEPTH = 2, ORA_SIGMA = 3, ORA_DEPTH_CHECKED = 4, ORA_POINTS = 5 };
 int ora_get_plane(void* h, int kf_id, int what, float* out); /* H*W floats, POINTS: H*3W */

@@ -58,6 +58,8 @@ def lib():
         L.ora_semidense.argtypes = [vp, C.c_int, ip, fp, C.c_int, C.c_float, C.c_float]
         L.ora_interkf.argtypes = [vp, C.c_int, ip, C.c_int]
         L.ora_pointset.argtypes = [vp, C.c_int]
+        L.ora_set_maps.argtypes = [vp, C.c_int, vp, vp]
+        L.ora_confident_points.argtypes = [vp, C.c_int, C.c_double, C.c_int, C.c_int, vp, vp, vp]
         L.ora_get_plane.argtypes = [vp, C.c_int, C.c_int, vp]
         L.ora_get_istddev.argtypes = [vp, C.c_int]
         L.ora_get_istddev.restype = C.c_float
@@ -158,6 +160,22 @@ class Oracle:
 
     def pointset(self, kf_id):
         assert self.L.ora_pointset(self.h, kf_id) == 0
+
+    def set_maps(self, kf_id, depth, sigma):
+        d = np.ascontiguousarray(depth, np.float32)
+        s = np.ascontiguousarray(sigma, np.float32)
+        assert self.L.ora_set_maps(self.h, kf_id, d.ctypes.data, s.ctypes.data) == 0
+
+    def confident_points(self, kf_id, max_sigma=0.01, max_points=0):
+        h, w = self.shape[kf_id]
+        cap = h * w
+        xyz = np.empty((cap, 3), np.float32)
+        sig = np.empty(cap, np.float32)
+        pix = np.empty(cap, np.uint32)
+        n = self.L.ora_confident_points(self.h, kf_id, float(max_sigma), int(max_points), cap, xyz.ctypes.data, sig.ctypes.data,
+                                        pix.ctypes.data)
+        assert n >= 0, n
+        return xyz[:n].copy(), sig[:n].copy(), pix[:n].copy(), n
 
     def plane(self, kf_id, what):
         h, w = self.shape[kf_id]

@@ -56,6 +56,8 @@ SYMBOLS = {
     "sd_semidense": (C.c_int, [_vp, C.c_int, _ip, _fp, C.c_int, C.c_float, C.c_float]),
     "sd_interkf_check": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
     "sd_update_pointset": (C.c_int, [_vp, C.c_int]),
+    "sd_confident_points": (C.c_int, [_vp, C.c_int, C.c_double, C.c_int, C.c_int, _vp, _vp, _vp, _ip]),
+    "sd_confident_points_device": (C.c_int, [_vp, C.c_int, C.c_double, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _ip, _ip]),
     "sd_download": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
     "sd_download_async": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
     "sd_download_plane": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
@@ -212,6 +214,27 @@ class Context:
 
     def update_pointset(self, kf_id):
         self._ck(self.L.sd_update_pointset(self.h, int(kf_id)))
+
+    def confident_points(self, kf_id, max_sigma=0.01, max_points=0, capacity=None):
+        """(xyz [n,3], sigma [n], pixel [n] = y << 16 | x, count) of the pixels PM.cc:120-121 keeps; see sd_confident_points."""
+        h, w = self.shape
+        cap = int(capacity) if capacity is not None else (int(max_points) if 0 < max_points < h * w else h * w)
+        xyz = np.empty((cap, 3), np.float32)
+        sig = np.empty(cap, np.float32)
+        pix = np.empty(cap, np.uint32)
+        n = C.c_int()
+        self._ck(self.L.sd_confident_points(self.h, int(kf_id), float(max_sigma), int(max_points), cap, xyz.ctypes.data,
+                                            sig.ctypes.data, pix.ctypes.data, C.byref(n)))
+        m = min(n.value, cap)
+        return xyz[:m], sig[:m], pix[:m], n.value
+
+    def confident_points_device(self, kf_id, max_sigma=0.01, max_points=0):
+        """Device pointers (xyz, sigma, pixel) into the context's scratch + (selected, confident) counts."""
+        px, ps, pp = _vp(), _vp(), _vp()
+        n, nc = C.c_int(), C.c_int()
+        self._ck(self.L.sd_confident_points_device(self.h, int(kf_id), float(max_sigma), int(max_points), C.byref(px), C.byref(ps),
+                                                   C.byref(pp), C.byref(n), C.byref(nc)))
+        return px.value, ps.value, pp.value, n.value, nc.value
 
     def download(self, kf_id, points=False):
         h, w = self.shape

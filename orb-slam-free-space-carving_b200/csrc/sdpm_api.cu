@@ -36,6 +36,7 @@ struct Slot {
     uint32_t* list = nullptr;   // active pixels (k0_gradient), input of k1_search
     uint32_t* vlist = nullptr;  // pixels carrying a depth after the intra-KF stage (k23_intra), input of k4_inter_check
     KfMeta* meta = nullptr;
+    int* h_active = nullptr;    // pinned host copy of meta->active_count, valid once ev_up has completed
     bool vlist_ok = false;      // vlist / meta->valid_count describe `depth`
     bool has_semidense = false, has_checked = false, has_points = false, pose_changed = false;
     cudaEvent_t ev_up = nullptr;  // upload + K0 done (s_up)
@@ -85,6 +86,14 @@ struct sd_ctx {
     uint64_t t_n[T_COUNT] = {0};
     float chi_fuse_f = 0, chi_inter_f = 0;
     int sm_count = 0, k1_grid = 0;  // persistent k1_search grid: SMs x resident blocks
+    // K6 scratch (confident-point feed), grown on demand
+    K6State* conf_state = nullptr;
+    uint32_t* conf_hist = nullptr;
+    int* conf_seg = nullptr;      // 4 x nseg ints
+    uint8_t* conf_out = nullptr;  // cap x (xyz, sigma, pixel)
+    int conf_cap = 0;
+    int* h_conf = nullptr;        // pinned: {total, confident}
+    int k1_tasks_per_warp = 0;      // > 0: k1_search warps retire after this many tasks (grid sized to the list), 0: persistent
 };
 
 namespace {
@@ -140,6 +149,7 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->list = (uint32_t*)p; p += lplane;
     s->vlist = (uint32_t*)p; p += lplane;
     s->meta = (KfMeta*)p;
+    if (cudaHostAlloc(&s->h_active, sizeof(int), cudaHostAllocDefault) != cudaSuccess) s->h_active = nullptr;
     cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_dn, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_sd, cudaEventDisableTiming);
@@ -152,6 +162,7 @@ void free_slot(Slot* s) {
     if (!s) return;
     cudaFree(s->slab);
     cudaFree(s->points);
+    if (s->h_active) cudaFreeHost(s->h_active);
     if (s->ev_up) cudaEventDestroy(s->ev_up);
     if (s->ev_dn) cudaEventDestroy(s->ev_dn);
     if (s->ev_sd) cudaEventDestroy(s->ev_sd);
@@ -265,6 +276,8 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
     k0_finalize<<<1, 1, 0, c->s_up>>>(s->meta, w, h);
     c->launches++;
     CU(c, cudaGetLastError());
+    // the list length travels to the host so that later launches over the list can be sized to it
+    if (s->h_active) CU(c, cudaMemcpyAsync(s->h_active, &s->meta->active_count, sizeof(int), cudaMemcpyDeviceToHost, c->s_up));
     CU(c, cudaEventRecord(s->ev_up, c->s_up));
     return SD_OK;
 }
@@ -293,6 +306,7 @@ void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
     A.task_counter = &s->meta->k1_task;
     A.hyp = nullptr; A.hyp_stride = 0;
     A.probe_out = nullptr;
+    A.max_tasks = 0xffffffffu;
 }
 
 void fill_nbr(Slot* s, Slot* nb, float rot, NbrConst& N) {
@@ -373,6 +387,8 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
         int use = per_sm;
         if (const char* e = getenv("SDPM_K1_BLOCKS_PER_SM")) use = std::max(1, std::min(per_sm, atoi(e)));
         c->k1_grid = c->sm_count * use;
+        c->k1_tasks_per_warp = K1_TASKS_PER_WARP_DEFAULT;
+        if (const char* e = getenv("SDPM_K1_TASKS_PER_WARP")) c->k1_tasks_per_warp = std::max(0, atoi(e));
         for (int i = 0; i < sd_ctx::RING; ++i)
             if (cudaEventCreateWithFlags(&c->ev_ring[i], cudaEventDisableTiming) != cudaSuccess) {
                 delete c;
@@ -402,6 +418,11 @@ int sd_destroy(sd_ctx* c) {
     if (c->ev_tmp) cudaEventDestroy(c->ev_tmp);
     if (c->ev_span_a) cudaEventDestroy(c->ev_span_a);
     if (c->ev_span_b) cudaEventDestroy(c->ev_span_b);
+    cudaFree(c->conf_state);
+    cudaFree(c->conf_hist);
+    cudaFree(c->conf_seg);
+    cudaFree(c->conf_out);
+    if (c->h_conf) cudaFreeHost(c->h_conf);
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_main);
     cudaStreamDestroy(c->s_srch);
@@ -482,8 +503,21 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     if (c->hypfree_valid[hb]) CU(c, cudaStreamWaitEvent(c->s_srch, c->ev_hypfree[hb], 0));
     CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), c->s_srch));
     {
+        // Blocks that retire after a bounded number of tasks let the high-priority kernels of the previous key
+        // frames (s_main, s_chk) onto the SMs while the search is still running; the grid covers the list
+        // length when the host already knows it (K0 finished), else the list's capacity.
+        int grid = c->k1_grid;
+        A.max_tasks = 0xffffffffu;
+        if (c->k1_tasks_per_warp > 0) {
+            long long cap = (long long)(c->W - 2 * c->P.border) * (c->H - 2 * c->P.border);
+            if (s->h_active && cudaEventQuery(s->ev_up) == cudaSuccess) cap = std::max(0, *s->h_active);
+            const long long ntask = ((cap + 31) / 32) * n;
+            const long long per_block = (long long)K1_WARPS * c->k1_tasks_per_warp;
+            grid = (int)std::max(1ll, (ntask + per_block - 1) / per_block);
+            A.max_tasks = (unsigned)c->k1_tasks_per_warp;
+        }
         ScopedTimer t(c, c->s_srch, T_SEARCH);
-        k1_search<<<c->k1_grid, K1_WARPS * 32, 0, c->s_srch>>>(A);
+        k1_search<<<grid, K1_WARPS * 32, 0, c->s_srch>>>(A);
     }
     CU(c, cudaEventRecord(c->ev_srch[hb], c->s_srch));
     // ---- main stream: fusion into the scratch planes (zero = no depth), then k23_intra reads them with a
@@ -622,6 +656,95 @@ int sd_update_pointset(sd_ctx* c, int kf_id) {
     s->chk_recorded = true;
     s->has_points = true;
     s->pose_changed = false;
+    return SD_OK;
+}
+
+int sd_confident_points_device(sd_ctx* c, int kf_id, double max_sigma, int max_points, const float** xyz_dev, const float** sigma_dev,
+                               const uint32_t** pixel_dev, int* count, int* confident) {
+    if (!c || !count) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    const int npix = c->W * c->H;
+    const int cap = (max_points > 0 && max_points < npix) ? max_points : npix;
+    const int nseg_row = (c->W + 255) / 256, nseg = nseg_row * c->H;
+    if (!c->conf_state) {
+        CU(c, cudaMalloc(&c->conf_state, sizeof(K6State)));
+        CU(c, cudaMalloc(&c->conf_hist, 2 * 65536 * sizeof(uint32_t)));
+        CU(c, cudaMalloc(&c->conf_seg, (size_t)4 * nseg * sizeof(int)));
+        CU(c, cudaHostAlloc(&c->h_conf, 2 * sizeof(int), cudaHostAllocDefault));
+    }
+    if (c->conf_cap < cap) {
+        CU(c, cudaStreamSynchronize(c->s_chk));
+        cudaFree(c->conf_out);
+        c->conf_out = nullptr;
+        c->conf_cap = 0;
+        CU(c, cudaMalloc(&c->conf_out, (size_t)cap * 5 * sizeof(float)));
+        c->conf_cap = cap;
+    }
+    cudaStream_t st = c->s_chk;
+    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(st, s->ev_sd, 0));
+    ConfArgs A;
+    A.P.W = c->W; A.P.H = c->H; A.P.pitch_f = c->pitch_f;
+    A.P.fx = s->K[0]; A.P.fy = s->K[1]; A.P.cx = s->K[2]; A.P.cy = s->K[3];
+    std::memcpy(A.P.Twc, s->Twc, sizeof(A.P.Twc));
+    A.P.depth = s->has_checked ? s->depth_chk : s->depth;
+    A.P.points = nullptr;
+    A.sigma = s->sigma;
+    A.max_sigma = max_sigma;
+    A.max_points = max_points;
+    A.nseg_row = nseg_row; A.nseg = nseg;
+    A.st = c->conf_state;
+    A.hist = c->conf_hist;
+    A.seg_lt = c->conf_seg; A.seg_eq = c->conf_seg + nseg; A.seg_off = c->conf_seg + 2 * nseg; A.seg_eqoff = c->conf_seg + 3 * nseg;
+    A.out_xyz = (float*)c->conf_out;
+    A.out_sigma = A.out_xyz + (size_t)3 * c->conf_cap;
+    A.out_pix = (uint32_t*)(A.out_sigma + c->conf_cap);
+    A.cap = cap;
+    CU(c, cudaMemsetAsync(c->conf_state, 0, sizeof(K6State), st));
+    const dim3 blk(256), grd((c->W + 31) / 32, (c->H + 7) / 8);
+    CU(c, cudaMemsetAsync(c->conf_hist, 0, 2 * 65536 * sizeof(uint32_t), st));
+    k6_hist16<0><<<grd, blk, 0, st>>>(A);
+    k6_pick16<0><<<1, 1024, 0, st>>>(A);
+    c->launches += 2;
+    if (max_points > 0 && max_points < npix) {
+        k6_hist16<1><<<grd, blk, 0, st>>>(A);
+        k6_pick16<1><<<1, 1024, 0, st>>>(A);
+        c->launches += 2;
+    }
+    k6_count<<<(nseg + 7) / 8, 256, 0, st>>>(A);
+    k6_scan<<<1, 1024, 0, st>>>(A);
+    k6_write<<<(nseg + 7) / 8, 256, 0, st>>>(A);
+    c->launches += 3;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(&c->h_conf[0], &c->conf_state->total, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(c, cudaMemcpyAsync(&c->h_conf[1], &c->conf_state->confident, sizeof(int), cudaMemcpyDeviceToHost, st));
+    CU(c, cudaEventRecord(s->ev_chk, st));
+    s->chk_recorded = true;
+    CU(c, cudaStreamSynchronize(st));
+    *count = c->h_conf[0];
+    if (confident) *confident = c->h_conf[1];
+    if (xyz_dev) *xyz_dev = A.out_xyz;
+    if (sigma_dev) *sigma_dev = A.out_sigma;
+    if (pixel_dev) *pixel_dev = A.out_pix;
+    return SD_OK;
+}
+
+int sd_confident_points(sd_ctx* c, int kf_id, double max_sigma, int max_points, int capacity, float* xyz, float* sigma, uint32_t* pixel,
+                        int* count) {
+    if (!c || !count || capacity < 0) return SD_ERR_INVALID_ARG;
+    const float *dx = nullptr, *ds = nullptr;
+    const uint32_t* dp = nullptr;
+    int rc = sd_confident_points_device(c, kf_id, max_sigma, max_points, &dx, &ds, &dp, count, nullptr);
+    if (rc != SD_OK) return rc;
+    const size_t n = (size_t)std::min(*count, capacity);
+    if (n) {
+        if (xyz) CU(c, cudaMemcpyAsync(xyz, dx, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->s_chk));
+        if (sigma) CU(c, cudaMemcpyAsync(sigma, ds, n * sizeof(float), cudaMemcpyDeviceToHost, c->s_chk));
+        if (pixel) CU(c, cudaMemcpyAsync(pixel, dp, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->s_chk));
+        CU(c, cudaStreamSynchronize(c->s_chk));
+    }
     return SD_OK;
 }
 

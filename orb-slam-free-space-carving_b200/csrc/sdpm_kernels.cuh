@@ -66,6 +66,7 @@ struct SearchArgs {
     const KfMeta* meta;
     int count_override;  // >= 0: use instead of meta->active_count (probes)
     unsigned int* task_counter;  // zeroed before the launch; warps draw 32-entry tasks from it
+    unsigned int max_tasks;      // a warp retires after this many tasks (0xffffffff: persistent warps)
     float2* hyp;       // nullable; hypothesis buffer [neighbour][hyp_stride]: (rho, sigma), or (-1, 0) for none
     int hyp_stride;
     float* probe_out;  // nullable; [entry][6] = {rho, sigma, best uj, supported, best_u, best_v} of neighbour 0
@@ -497,6 +498,9 @@ constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller st
 #ifndef K1_MIN_BLOCKS
 #define K1_MIN_BLOCKS 5
 #endif
+#ifndef K1_TASKS_PER_WARP_DEFAULT
+#define K1_TASKS_PER_WARP_DEFAULT 0
+#endif
 #define K1_TIE_REL 2e-6f            // float shortcut of err: two candidates closer than this are re-scanned exactly
 #define K1_ERR_LIMIT_LO 999000.0f   // PM.cc:437 initial best_match_err = 1e6
 
@@ -546,7 +550,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
   // pixel's work) that the last warps to finish do not leave the machine idle for long.
   const unsigned nblk = ((unsigned)count + 31u) >> 5;
   const unsigned long long ntask = (unsigned long long)nblk * (unsigned)A.n;
-  for (;;) {
+  for (unsigned drawn = 0; drawn < A.max_tasks; ++drawn) {
     unsigned task = 0;
     if (lane == 0) task = atomicAdd(A.task_counter, 1u);
     task = __shfl_sync(full, task, 0);
@@ -1215,24 +1219,246 @@ __global__ void __launch_bounds__(128, K4_MIN_BLOCKS) k4_inter_check(const __gri
 // ------------------------------------------------------------------------------------------------
 // K5: UpdateSemiDensePointSet, PM.cc:337-367.  Twc*Pc: 4x4*4x1 small gemm, float left to right.
 // ------------------------------------------------------------------------------------------------
+// world point of pixel (x, y) with inverse depth inv_d, PM.cc:349-363; zeros outside the 2-px frame or without depth
+__device__ __forceinline__ void backproject(const PointArgs& A, int x, int y, float inv_d, float& p0, float& p1, float& p2) {
+    p0 = p1 = p2 = 0.f;
+    if (x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2 && inv_d > SD_EPS_F) {
+        const float Z = 1 / inv_d;
+        const float X = Z * ((float)x - A.cx) / A.fx;
+        const float Y = Z * ((float)y - A.cy) / A.fy;
+        p0 = A.Twc[0] * X + A.Twc[1] * Y + A.Twc[2] * Z + A.Twc[3] * 1.0f;
+        p1 = A.Twc[4] * X + A.Twc[5] * Y + A.Twc[6] * Z + A.Twc[7] * 1.0f;
+        p2 = A.Twc[8] * X + A.Twc[9] * Y + A.Twc[10] * Z + A.Twc[11] * 1.0f;
+    }
+}
+
 __global__ void __launch_bounds__(256) k5_pointset(const PointArgs A) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y * blockDim.y + threadIdx.y;
     if (x >= A.W || y >= A.H) return;
-    float p0 = 0.f, p1 = 0.f, p2 = 0.f;
-    if (x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2) {
-        const float inv_d = A.depth[(size_t)y * A.pitch_f + x];
-        if (inv_d > SD_EPS_F) {
-            const float Z = 1 / inv_d;
-            const float X = Z * ((float)x - A.cx) / A.fx;
-            const float Y = Z * ((float)y - A.cy) / A.fy;
-            p0 = A.Twc[0] * X + A.Twc[1] * Y + A.Twc[2] * Z + A.Twc[3] * 1.0f;
-            p1 = A.Twc[4] * X + A.Twc[5] * Y + A.Twc[6] * Z + A.Twc[7] * 1.0f;
-            p2 = A.Twc[8] * X + A.Twc[9] * Y + A.Twc[10] * Z + A.Twc[11] * 1.0f;
-        }
-    }
+    float p0, p1, p2;
+    backproject(A, x, y, A.depth[(size_t)y * A.pitch_f + x], p0, p1, p2);
     float* o = A.points + ((size_t)y * A.W + x) * 3;
     o[0] = p0; o[1] = p1; o[2] = p2;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6: confident-point feed.  The reference selects the points it trusts with
+// `depth_sigma_ > 0.01 -> skip; depth_map_ > 0.000001 -> keep` (PM.cc:120-121, whole image, raster
+// order) and the CARV transcript ingests extra 3-D points as a list per key frame
+// (SFMTranscriptInterface_ORBSLAM.cpp:319-374).  K6 compacts those pixels on the device, in raster
+// order (deterministic), optionally keeping only the `max_points` with the smallest sigma (exact
+// radix select over the float bits, ties admitted in raster order), and back-projects them with
+// the arithmetic of K5 -- so only count*12 bytes cross PCIe instead of three full planes.
+//
+//   k6_hist16 (x2)  histogram of the selection key's high / low 16 bits   } only when max_points > 0
+//   k6_pick16 (x2)  locate the bin of the max_points-th smallest key      }
+//   k6_count        per 256-pixel raster segment: keys below / equal to the threshold
+//   k6_scan         exclusive scan over the segments -> output offsets, total
+//   k6_write        compacted (x, y, z), sigma, pixel index
+// ------------------------------------------------------------------------------------------------
+struct K6State {
+    int select;         // 1: only keys < thr, and the first eq_take keys == thr, are admitted
+    uint32_t thr;       // selection key of the max_points-th smallest sigma
+    int eq_take;
+    uint32_t prefix;    // radix select: high 16 bits fixed by pass 0
+    int k_rem;          // radix select: rank still to find inside the current bin
+    int total;          // admitted points (written by k6_scan)
+    int confident;      // pixels passing the reference predicate (before the top-k cut)
+};
+
+struct ConfArgs {
+    PointArgs P;             // depth plane + intrinsics + Twc
+    const float* sigma;
+    double max_sigma;        // PM.cc:120 compares the float with a double literal
+    int max_points;          // <= 0: no cut
+    int nseg_row, nseg;      // 256-pixel segments per row / in the image
+    K6State* st;
+    uint32_t* hist;          // [2][65536]
+    int* seg_lt;             // [nseg] keys below the threshold (all confident pixels when !select)
+    int* seg_eq;             // [nseg] keys equal to the threshold
+    int* seg_off;            // [nseg] output offset of the segment
+    int* seg_eqoff;          // [nseg] equal keys before the segment
+    float* out_xyz;          // [cap][3]
+    float* out_sigma;        // [cap]
+    uint32_t* out_pix;       // [cap] y << 16 | x
+    int cap;
+};
+
+// total order on floats as unsigned keys (negative < positive, NaNs at the ends)
+__device__ __forceinline__ uint32_t sigma_key(uint32_t bits) { return bits ^ ((uint32_t)((int32_t)bits >> 31) | 0x80000000u); }
+// The bits of a float as an integer the compiler cannot trace back to the float: nvcc otherwise turns the sign-bit
+// arithmetic of sigma_key into FADD -|x|, -0, which canonicalises NaN payloads and signs (seen in SASS; NaN sigmas
+// pass the reference's `sigma > 0.01` test, so they are part of the selection and need a defined place in the order)
+__device__ __forceinline__ uint32_t raw_bits(float v) {
+    uint32_t b;
+    asm volatile("mov.b32 %0, %1;" : "=r"(b) : "f"(v));
+    return b;
+}
+
+__device__ __forceinline__ bool k6_confident(const ConfArgs& A, int x, int y, float& d, float& s) {
+    const size_t o = (size_t)y * A.P.pitch_f + x;
+    s = __ldg(A.sigma + o);
+    d = __ldg(A.P.depth + o);
+    return !((double)s > A.max_sigma) && d > SD_EPS_F;  // PM.cc:120-121
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(256) k6_hist16(const ConfArgs A) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= A.P.W || y >= A.P.H) return;
+    float d, s;
+    if (!k6_confident(A, x, y, d, s)) return;
+    const uint32_t key = sigma_key(raw_bits(s));
+    if (PASS == 0) atomicAdd(A.hist + (key >> 16), 1u);
+    else if (A.st->select && (key >> 16) == A.st->prefix) atomicAdd(A.hist + 65536 + (key & 0xffffu), 1u);
+}
+
+// one block of 1024 threads: find the bin holding rank k_rem (1-based) of the 65536-bin histogram
+template <int PASS>
+__global__ void __launch_bounds__(1024) k6_pick16(const ConfArgs A) {
+    __shared__ unsigned int s_part[1024];
+    __shared__ unsigned int s_tot;
+    const int t = threadIdx.x;
+    const uint32_t* h = A.hist + PASS * 65536;
+    unsigned int loc = 0;
+    for (int i = 0; i < 64; ++i) loc += h[t * 64 + i];
+    s_part[t] = loc;
+    __syncthreads();
+    if (t == 0) {
+        unsigned int acc = 0;
+        for (int i = 0; i < 1024; ++i) { const unsigned int v = s_part[i]; s_part[i] = acc; acc += v; }
+        s_tot = acc;
+    }
+    __syncthreads();
+    K6State* st = A.st;
+    if (PASS == 0 && t == 0) {
+        st->confident = (int)s_tot;
+        st->select = (A.max_points > 0 && s_tot > (unsigned)A.max_points) ? 1 : 0;
+        st->k_rem = A.max_points;
+        st->eq_take = 0;
+        st->thr = 0;
+    }
+    __syncthreads();
+    if (!st->select) return;
+    const unsigned int k = (unsigned)st->k_rem;  // read before anyone writes it (only the owner thread below writes)
+    __syncthreads();
+    const unsigned int before = s_part[t];
+    if (k > before && k <= before + loc) {  // exactly one thread
+        unsigned int acc = before;
+        for (int i = 0; i < 64; ++i) {
+            const unsigned int v = h[t * 64 + i];
+            if (k <= acc + v) {
+                const uint32_t bin = (uint32_t)(t * 64 + i);
+                if (PASS == 0) { st->prefix = bin; st->k_rem = (int)(k - acc); }
+                else { st->thr = (st->prefix << 16) | bin; st->eq_take = (int)(k - acc); }
+                break;
+            }
+            acc += v;
+        }
+    }
+}
+
+// one warp per 256-pixel raster segment
+__global__ void __launch_bounds__(256) k6_count(const ConfArgs A) {
+    const int seg = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (seg >= A.nseg) return;
+    const int y = seg / A.nseg_row, xs = (seg - y * A.nseg_row) * 256;
+    const int select = A.st->select;
+    const uint32_t thr = A.st->thr;
+    int nlt = 0, neq = 0;
+    for (int i = 0; i < 8; ++i) {
+        const int x = xs + i * 32 + lane;
+        float d, s;
+        bool lt = false, eq = false;
+        if (x < A.P.W && k6_confident(A, x, y, d, s)) {
+            const uint32_t key = sigma_key(raw_bits(s));
+            lt = !select || key < thr;
+            eq = select && key == thr;
+        }
+        nlt += __popc(__ballot_sync(0xffffffffu, lt));
+        neq += __popc(__ballot_sync(0xffffffffu, eq));
+    }
+    if (lane == 0) { A.seg_lt[seg] = nlt; A.seg_eq[seg] = neq; }
+}
+
+// single block: admitted points per segment = lt + clamp(eq_take - equal keys before, 0, eq); exclusive scans
+__global__ void __launch_bounds__(1024) k6_scan(const ConfArgs A) {
+    __shared__ int s_a[1024], s_e[1024];
+    __shared__ int s_carry_a, s_carry_e;
+    const int t = threadIdx.x;
+    const int eq_take = A.st->select ? A.st->eq_take : 0;
+    if (t == 0) { s_carry_a = 0; s_carry_e = 0; }
+    __syncthreads();
+    for (int base = 0; base < A.nseg; base += 1024) {
+        const int i = base + t;
+        const int e = i < A.nseg ? A.seg_eq[i] : 0;
+        // inclusive scan of the equal counts first: the admitted count of a segment depends on it
+        s_e[t] = e;
+        __syncthreads();
+        for (int d = 1; d < 1024; d <<= 1) {
+            const int v = t >= d ? s_e[t - d] : 0;
+            __syncthreads();
+            s_e[t] += v;
+            __syncthreads();
+        }
+        const int eq_before = s_carry_e + s_e[t] - e;
+        int adm = 0;
+        if (i < A.nseg) {
+            int take = eq_take - eq_before;
+            take = take < 0 ? 0 : (take > e ? e : take);
+            adm = A.seg_lt[i] + take;
+            A.seg_eqoff[i] = eq_before;
+        }
+        s_a[t] = adm;
+        __syncthreads();
+        for (int d = 1; d < 1024; d <<= 1) {
+            const int v = t >= d ? s_a[t - d] : 0;
+            __syncthreads();
+            s_a[t] += v;
+            __syncthreads();
+        }
+        if (i < A.nseg) A.seg_off[i] = s_carry_a + s_a[t] - adm;
+        __syncthreads();
+        if (t == 1023) { s_carry_a += s_a[1023]; s_carry_e += s_e[1023]; }
+        __syncthreads();
+    }
+    if (t == 0) A.st->total = s_carry_a;
+}
+
+__global__ void __launch_bounds__(256) k6_write(const ConfArgs A) {
+    const int seg = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (seg >= A.nseg) return;
+    const int y = seg / A.nseg_row, xs = (seg - y * A.nseg_row) * 256;
+    const int select = A.st->select, eq_take = A.st->eq_take;
+    const uint32_t thr = A.st->thr;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    int pos = A.seg_off[seg], eqn = A.seg_eqoff[seg];
+    for (int i = 0; i < 8; ++i) {
+        const int x = xs + i * 32 + lane;
+        float d = 0.f, s = 0.f;
+        bool lt = false, eq = false;
+        if (x < A.P.W && k6_confident(A, x, y, d, s)) {
+            const uint32_t key = sigma_key(raw_bits(s));
+            lt = !select || key < thr;
+            eq = select && key == thr;
+        }
+        const unsigned beq = __ballot_sync(0xffffffffu, eq);
+        const bool adm = lt || (eq && eqn + __popc(beq & lt_mask) < eq_take);
+        const unsigned badm = __ballot_sync(0xffffffffu, adm);
+        if (adm) {
+            const int o = pos + __popc(badm & lt_mask);
+            if (o < A.cap) {
+                float p0, p1, p2;
+                backproject(A.P, x, y, d, p0, p1, p2);
+                A.out_xyz[3 * (size_t)o] = p0; A.out_xyz[3 * (size_t)o + 1] = p1; A.out_xyz[3 * (size_t)o + 2] = p2;
+                A.out_sigma[o] = s;
+                A.out_pix[o] = ((uint32_t)y << 16) | (uint32_t)x;
+            }
+        }
+        pos += __popc(badm);
+        eqn += __popc(beq);
+    }
 }
 
 // pack / unpack between pitched planes and tight W*H buffers (NCCL halo exchange)

@@ -216,27 +216,39 @@ void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
           "sd_download");
 }
 
+int ProbabilityMapping::ConfidentPoints(KeyFrameView* kf, std::vector<Point3f>& out, double max_sigma, int max_points) {
+    if (kf->poseChanged) {  // PM.cc:329-331: points follow the current pose
+        check(sd_set_pose(ctx_, kf->mnId, kf->Tcw), "sd_set_pose");
+        kf->poseChanged = false;
+    }
+    const int npix = kf->im_.rows * kf->im_.cols;
+    int cap = (max_points > 0 && max_points < npix) ? max_points : 0, n = 0;
+    static_assert(sizeof(Point3f) == 3 * sizeof(float), "Point3f must be three packed floats");
+    const size_t base = out.size();
+    if (cap == 0) {  // size the buffer to the selection: count first (device-resident result), then copy
+        check(sd_confident_points(ctx_, kf->mnId, max_sigma, max_points, 0, nullptr, nullptr, nullptr, &cap), "sd_confident_points");
+        if (cap == 0) return 0;
+    }
+    out.resize(base + (size_t)cap);
+    check(sd_confident_points(ctx_, kf->mnId, max_sigma, max_points, cap, &out[base].x, nullptr, nullptr, &n), "sd_confident_points");
+    if (n < cap) out.resize(base + (size_t)n);
+    return n;
+}
+
 bool ProbabilityMapping::SavePointCloudObj(const std::string& path, double max_sigma) {
     std::FILE* f = std::fopen(path.c_str(), "w");
     if (!f) {
         std::fprintf(stderr, "Failed to save points on line\n");  // PM.cc:103
         return false;
     }
+    std::vector<Point3f> pts;
     for (KeyFrameView* kf : mpMap->GetAllKeyFrames()) {
         if (kf->isBad()) continue;
         if (!kf->semidense_flag_) continue;
         if (!kf->interKF_depth_flag_) continue;
-        const int rows = kf->im_.rows, cols = kf->im_.cols;
-        if (kf->SemiDensePointSets_.size() != (size_t)3 * rows * cols) continue;
-        for (int y = 0; y < rows; y++)
-            for (int x = 0; x < cols; x++) {
-                const size_t o = (size_t)y * cols + x;
-                if (kf->depth_sigma_[o] > max_sigma) continue;
-                if (kf->depth_map_[o] > 0.000001) {
-                    const float* P = &kf->SemiDensePointSets_[(size_t)y * 3 * cols + 3 * x];
-                    std::fprintf(f, "v %f %f %f\n", P[0], P[1], P[2]);  // std::to_string(float) == "%f"
-                }
-            }
+        pts.clear();
+        ConfidentPoints(kf, pts, max_sigma, 0);  // PM.cc:114-127 on the device
+        for (const Point3f& P : pts) std::fprintf(f, "v %f %f %f\n", P.x, P.y, P.z);  // std::to_string(float) == "%f"
     }
     std::fclose(f);
     return true;

@@ -43,6 +43,10 @@ struct PlaneView {
     bool empty() const { return !data || rows <= 0 || cols <= 0; }
 };
 
+struct Point3f {  // cv::Point3f stand-in
+    float x, y, z;
+};
+
 // What PM.cc reads from / writes to ORB_SLAM2::KeyFrame.
 struct KeyFrameView {
     int mnId = -1;
@@ -109,7 +113,13 @@ public:
     void InterKeyFrameDepthChecking(KeyFrameView* currentKf, std::vector<KeyFrameView*> neighbors);
 
     // PM.cc:100-132: "v x y z" for every pixel with sigma <= 0.01 (PM.cc:120) and inverse depth > 1e-6.
+    // The selection runs on the device (sd_confident_points); only the selected points cross PCIe.
     bool SavePointCloudObj(const std::string& path, double max_sigma = 0.01);
+    // The same selection for one key frame as the point list the CARV transcript ingests
+    // (SFMTranscriptInterface_ORBSLAM::addKeyFrameInsertionWithLinesEntry(k, kCopy, std::vector<cv::Point3f>&),
+    // SFMTranscriptInterface_ORBSLAM.cpp:319-374); max_points > 0 keeps the max_points smallest-sigma points.
+    // Returns the number of points appended to `out`.
+    int ConfidentPoints(KeyFrameView* kf, std::vector<Point3f>& out, double max_sigma = 0.01, int max_points = 0);
 
     // ComputeFundamental (PM.cc:972-987) and GetRotInPlane + median (PM.cc:467-484, 172-177):
     // private in PM.h, public here so the tests can reach them.

@@ -129,6 +129,11 @@ def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
     with open(obj_path) as f:
         lines = f.read().splitlines()
     assert len(lines) == n_obj and all(line.startswith("v ") for line in lines[:50])   # PM.cc:100-132
+    expected = []
+    for k in plan.ids:   # the device-side selection (sd_confident_points) writes what the oracle's PM.cc:114-127 loop selects
+        xyz = ora.confident_points(k, 0.05, 0)[0]
+        expected += ["v %f %f %f" % (float(p[0]), float(p[1]), float(p[2])) for p in xyz]
+    assert lines == expected
     nfound = 0
     for (i1, i2, x, y, mind, maxd, rot) in probes:
         rec = raw[off:off + 28].view(np.float32); off += 28
