@@ -486,7 +486,10 @@ __device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const flo
     return true;
 }
 
-constexpr int K1_WARPS = 8;
+#ifndef K1_WARPS_PER_BLOCK
+#define K1_WARPS_PER_BLOCK 8
+#endif
+constexpr int K1_WARPS = K1_WARPS_PER_BLOCK;
 constexpr int K1_QHALF = 512;           // what 16 lanes can queue in one scan step (16 lanes x 32 columns)
 constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller step is queued in two halves
 #ifndef K1F_MIN_BLOCKS
