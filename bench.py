@@ -169,7 +169,7 @@ def run_reference(args):
         "pixels_per_s": kfps * plan.scene.w * plan.scene.h,
         "note": "reference CPU algorithm = oracle/pm_oracle.cc (PM.cc is not compilable: SURVEY F1-F3); per-call cv::Mat churn hoisted, so faster than the literal reference",
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -236,6 +236,13 @@ def run_b200(args):
     def exchange():
         if world == 1:
             return 0
+        if os.environ.get("BENCH_SKIP_NCCL"):   # diagnostic: same packing / installing, no wire (results are then wrong at the seams)
+            for p, ids in shard.send.items():
+                pack(ids, p)
+            for p, ids in shard.recv.items():
+                for i, k in enumerate(ids):
+                    ctx.import_maps(k, recv_buf[p][i, 0].data_ptr(), recv_buf[p][i, 1].data_ptr())
+            return 0
         with torch.cuda.stream(ext):  # NCCL orders against the context's compute stream
             ops = []
             for p in sorted(set(shard.send) | set(shard.recv)):
@@ -251,6 +258,8 @@ def run_b200(args):
         return sum(t.numel() * 4 for t in list(send_buf.values()) + list(recv_buf.values()))
 
     last_needed = {k: int(max(gplan.nbrs[k].max(), k)) for k in owned}
+    schedule = sharding.pipelined_schedule(shard, lambda k: gplan.nbrs[k]) if world > 1 else None
+    plain_schedule = [("semidense", k) for k in owned] + [("exchange",)] + [("finish", k) for k in owned]
 
     def step(e2e):
         for k in resident:
@@ -277,17 +286,24 @@ def run_b200(args):
             for j in pending:
                 finish(j)
         else:
-            for k in owned:
-                mn, mx = gplan.prior[k]
-                ctx.semidense(k, gplan.nbrs[k], gplan.rots[k], mn, mx)
-            exchange()
-            for j in owned:
-                finish(j)
+            # boundary key frames first, one exchange, then the interior with the same software pipeline
+            # (sharding.pipelined_schedule): only the few key frames with halo neighbours wait for the peers
+            for op in (plain_schedule if os.environ.get("BENCH_PLAIN_SCHEDULE") else schedule):
+                if op[0] == "semidense":
+                    k = op[1]
+                    mn, mx = gplan.prior[k]
+                    ctx.semidense(k, gplan.nbrs[k], gplan.rots[k], mn, mx)
+                elif op[0] == "exchange":
+                    exchange()
+                else:
+                    finish(op[1])
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
+
+    host_issue_ms = []
 
     def timed(e2e, steps, warmup, sampler=None):
         for _ in range(warmup):
@@ -299,13 +315,17 @@ def run_b200(args):
         ctx.timing_reset()
         l0 = ctx.launch_count()
         ctx.span_begin()
+        t_host = time.perf_counter()
         for _ in range(steps):
             step(e2e)
+        host_issue_ms.append(1e3 * (time.perf_counter() - t_host))   # host time to ISSUE the steps (no device wait)
         ms = ctx.span_end()
         barrier()
         clocks = sampler.stop() if sampler else None
         launches = ctx.launch_count() - l0
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if os.environ.get("BENCH_VERBOSE"):
+            sys.stderr.write(f"rank {rank}: span {ms:.2f} ms for {steps} steps, host issue {host_issue_ms[-1]:.2f} ms\n")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, clocks
@@ -351,6 +371,7 @@ def run_b200(args):
             "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e / args.steps,
                     "h2d_bytes_per_step": len(resident) * img_bytes, "d2h_bytes_per_step": len(owned) * 2 * px * 4},
             "gpu_launches": int(launches),
+            "host_issue_ms_per_step": {"value": host_issue_ms[0] / args.steps, "e2e": host_issue_ms[1] / args.steps},
             "clocks": clocks,
             "roofline": {"kernel": "k1_search + k1_fuse (epipolar search + hypothesis fusion)", "bound": "hbm", "achieved": achieved,
                          "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
@@ -366,15 +387,34 @@ def run_b200(args):
             dt, _, _, threads = cpu_pass(po, synth, pipeline, args, sample)
             line["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"first {sample} key frames of the same workload, all stages K0..K5, oracle port with OpenMP on the reference's five pragma loops (one pass, {dt:.1f} s)"}
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_FD = None
+
+
+def emit(line):
+    """The ONE JSON line of the contract, on the real stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, data)
+
+
 def main():
+    global _JSON_FD
     args = parse()
+    # libraries print to stdout behind our back (NCCL: "NCCL version ..." at communicator creation): keep fd 1 for
+    # the JSON line only, everything else goes to stderr
+    sys.stdout.flush()
+    _JSON_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:

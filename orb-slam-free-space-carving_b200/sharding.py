@@ -92,3 +92,60 @@ def exchange_maps(plan: ShardPlan, dist, pack: Callable[[List[int]], "object"], 
     for ids, t in recv_bufs:
         unpack(ids, t)
     return nbytes
+
+
+def pipelined_schedule(plan: ShardPlan, neighbours: Callable[[int], np.ndarray]):
+    """Issue order of one rank's step that keeps the stream pipeline of the single-GPU path
+    (search | fuse+intra | inter+points) running across the halo exchange:
+
+        1. ("semidense", k) for the BOUNDARY key frames (the ones some peer needs), so their maps exist early;
+        2. ("exchange",)    the one point-to-point exchange step (send boundary maps, receive + install halo maps);
+        3. ("semidense", k) for the interior key frames, each followed by ("finish", j) -- inter-key-frame
+           check + point set -- for every owned j whose neighbours all have maps by then.
+
+    A "finish" is emitted only after the semidense of every OWNED neighbour and, for key frames with halo
+    neighbours, after the exchange.  Pure function of the plan: every rank derives it locally.
+    """
+    owned = list(plan.owned)
+    own = set(owned)
+    boundary = sorted({k for ids in plan.send.values() for k in ids})
+    bset = set(boundary)
+    order = boundary + [k for k in owned if k not in bset]
+    nb = {j: [int(v) for v in neighbours(j)] for j in owned}
+    waiting = {j: sum(1 for v in nb[j] if v in own) for j in owned}   # owned neighbours without maps yet
+    users = {}
+    for j in owned:
+        for v in nb[j]:
+            if v in own:
+                users.setdefault(v, []).append(j)
+    has_halo = {j: any(v not in own for v in nb[j]) for j in owned}
+    done_self = set()
+    ops, ready_wait_exchange = [], []
+    exchanged = not (plan.send or plan.recv)
+
+    def maybe_finish(j):
+        if waiting[j] == 0 and j in done_self:
+            if has_halo[j] and not exchanged:
+                ready_wait_exchange.append(j)
+            else:
+                ops.append(("finish", j))
+
+    for i, k in enumerate(order):
+        if i == len(boundary) and not exchanged:
+            ops.append(("exchange",))
+            exchanged = True
+            for j in ready_wait_exchange:
+                ops.append(("finish", j))
+            ready_wait_exchange = []
+        ops.append(("semidense", k))
+        done_self.add(k)
+        for j in users.get(k, []):
+            waiting[j] -= 1
+            if j != k:
+                maybe_finish(j)
+        maybe_finish(k)
+    if not exchanged:      # every owned key frame is a boundary key frame
+        ops.append(("exchange",))
+        for j in ready_wait_exchange:
+            ops.append(("finish", j))
+    return ops

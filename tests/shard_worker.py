@@ -47,9 +47,6 @@ def main():
     ctx = pkg.Context(local)
     for k in shard.resident:                              # owned + image halo: K0 is recomputed locally
         ctx.upload_keyframe(k, images[k], scene.K, plan.poses[k])
-    for k in shard.owned:
-        ctx.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
-
     ext = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
 
     def pack(ids):
@@ -71,11 +68,19 @@ def main():
         for i, k in enumerate(ids):
             ctx.import_maps(k, t[i, 0].data_ptr(), t[i, 1].data_ptr())
 
-    with torch.cuda.stream(ext):                          # NCCL orders against the context's compute stream
-        nbytes = sharding.exchange_maps(shard, dist, pack, alloc, unpack)
-    for k in shard.owned:
-        ctx.interkf_check(k, plan.nbrs[k])
-        ctx.update_pointset(k)
+    # the issue order bench.py uses: boundary key frames, the one exchange, then the interior with the
+    # inter-key-frame check of a key frame queued as soon as all its neighbours have maps
+    nbytes = 0
+    for op in sharding.pipelined_schedule(shard, lambda k: plan.nbrs[k]):
+        if op[0] == "semidense":
+            k = op[1]
+            ctx.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
+        elif op[0] == "exchange":
+            with torch.cuda.stream(ext):                  # NCCL orders against the context's compute stream
+                nbytes = sharding.exchange_maps(shard, dist, pack, alloc, unpack)
+        else:
+            ctx.interkf_check(op[1], plan.nbrs[op[1]])
+            ctx.update_pointset(op[1])
     ctx.sync()
 
     ora = po.Oracle(threads=max(1, po.lib().ora_max_threads() // world))

@@ -38,6 +38,39 @@ def test_plan_is_consistent(built, nkf, world, n):
             assert plans[peer].recv[p.rank] == ids
 
 
+@pytest.mark.parametrize("nkf,world,n", [(400, 2, 10), (1000, 8, 20), (37, 4, 6), (12, 2, 10), (50, 3, 40), (25, 1, 10)])
+def test_pipelined_schedule_respects_dependencies(built, nkf, world, n):
+    """Issue order of a rank's step (bench.py, N > 1): every owned key frame gets exactly one semidense and one
+    finish (inter-KF check + point set); the exchange comes after the semidense of everything this rank sends;
+    a finish comes after the semidense of all owned neighbours and, with halo neighbours, after the exchange;
+    interior finishes are interleaved with the remaining semidense calls (the pipeline keeps running)."""
+    sharding, synth = _mods(built)
+    nb = lambda k: synth.Scene.neighbours(k, nkf, n)
+    for r in range(world):
+        p = sharding.make_plan(nkf, world, r, nb)
+        ops = sharding.pipelined_schedule(p, nb)
+        own, sd, fin, exchanged = set(p.owned), [], [], False
+        early = 0
+        for op in ops:
+            if op[0] == "semidense":
+                sd.append(op[1])
+            elif op[0] == "exchange":
+                assert not exchanged
+                exchanged = True
+                assert all(k in sd for ids in p.send.values() for k in ids)
+            else:
+                j = op[1]
+                fin.append(j)
+                assert j in sd
+                for v in (int(v) for v in nb(j)):
+                    assert (v in sd) if v in own else exchanged, (r, j, v)
+                early += len(sd) < len(p.owned)
+        assert sorted(sd) == p.owned and sorted(fin) == p.owned
+        assert exchanged == (world > 1)
+        if len(p.owned) > 3 * n:
+            assert early > len(p.owned) // 2          # most checks are queued while searches are still being issued
+
+
 def test_interior_halo_size(built):
     sharding, synth = _mods(built)
     nb = lambda k: synth.Scene.neighbours(k, 1000, 20)
