@@ -242,8 +242,17 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         return fail(c, SD_ERR_SHAPE, "key frame %d is %dx%d, context is %dx%d", kf_id, w, h, c->W, c->H);
     }
     Slot* s = find(c, kf_id);
-    if (s) {
-        // planes are being replaced: wait for everything already queued that may still read them
+    bool fresh = false;
+    if (!s) {
+        fresh = c->free_slots.empty();
+        int rc = alloc_slot(c, &s);
+        if (rc != SD_OK) return rc;
+        s->id = kf_id;
+        c->kfs[kf_id] = s;
+    }
+    if (!fresh) {
+        // the planes are being replaced (same key frame again, or a slot recycled by sd_release_keyframe):
+        // wait for everything already queued that may still read them
         CU(c, cudaEventRecord(c->ev_tmp, c->s_main));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
         CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));
@@ -252,11 +261,6 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
         CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
-    } else {
-        int rc = alloc_slot(c, &s);
-        if (rc != SD_OK) return rc;
-        s->id = kf_id;
-        c->kfs[kf_id] = s;
     }
     s->has_semidense = s->has_checked = s->has_points = s->pose_changed = s->vlist_ok = false;
     s->dn_pending = false;
@@ -456,8 +460,8 @@ int sd_release_keyframe(sd_ctx* c, int kf_id) {
     if (!c) return SD_ERR_INVALID_ARG;
     auto it = c->kfs.find(kf_id);
     if (it == c->kfs.end()) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
-    CU(c, cudaSetDevice(c->device));
-    CU(c, cudaDeviceSynchronize());  // nothing queued may still reference the planes
+    // No synchronisation here: queued work may still read the planes, so the slot is only parked; whoever takes it
+    // from the free list (sd_upload_keyframe) first orders its writes after everything queued on the other streams.
     c->free_slots.push_back(it->second);
     c->kfs.erase(it);
     return SD_OK;
@@ -648,8 +652,8 @@ int sd_update_pointset(sd_ctx* c, int kf_id) {
     A.points = s->points;
     {
         ScopedTimer t(c, c->s_chk, T_POINTS);
-        dim3 blk(32, 8), grd((c->W + 31) / 32, (c->H + 7) / 8);
-        k5_pointset<<<grd, blk, 0, c->s_chk>>>(A);
+        dim3 grd((c->W + 255) / 256, c->H);
+        k5_pointset<<<grd, 256, 0, c->s_chk>>>(A);
     }
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_chk, c->s_chk));

@@ -1235,14 +1235,25 @@ __device__ __forceinline__ void backproject(const PointArgs& A, int x, int y, fl
     }
 }
 
+// One block = 256 consecutive pixels of one row.  The 768 output floats are staged in shared memory so that the
+// global stores are whole float4s (a thread's own 3 floats would be a 12-byte-stride store).
 __global__ void __launch_bounds__(256) k5_pointset(const PointArgs A) {
-    const int x = blockIdx.x * blockDim.x + threadIdx.x;
-    const int y = blockIdx.y * blockDim.y + threadIdx.y;
-    if (x >= A.W || y >= A.H) return;
-    float p0, p1, p2;
-    backproject(A, x, y, A.depth[(size_t)y * A.pitch_f + x], p0, p1, p2);
-    float* o = A.points + ((size_t)y * A.W + x) * 3;
-    o[0] = p0; o[1] = p1; o[2] = p2;
+    __shared__ __align__(16) float s_out[256 * 3];
+    const int x0 = blockIdx.x * 256, y = blockIdx.y;
+    const int x = x0 + threadIdx.x;
+    float p0 = 0.f, p1 = 0.f, p2 = 0.f;
+    if (x < A.W) backproject(A, x, y, __ldg(A.depth + (size_t)y * A.pitch_f + x), p0, p1, p2);
+    s_out[3 * threadIdx.x] = p0; s_out[3 * threadIdx.x + 1] = p1; s_out[3 * threadIdx.x + 2] = p2;
+    __syncthreads();
+    const int npx = min(256, A.W - x0);          // pixels of this block inside the row
+    float* row = A.points + ((size_t)y * A.W + x0) * 3;
+    if ((A.W & 3) == 0 && (reinterpret_cast<uintptr_t>(A.points) & 15) == 0 && (npx & 3) == 0) {
+        // row pitch 3W floats and x0*3 are multiples of 4 floats: aligned float4 stores
+        if (threadIdx.x < (npx * 3) / 4)
+            reinterpret_cast<float4*>(row)[threadIdx.x] = reinterpret_cast<const float4*>(s_out)[threadIdx.x];
+    } else {
+        for (int i = threadIdx.x; i < npx * 3; i += 256) row[i] = s_out[i];
+    }
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -357,3 +357,60 @@ def test_dense_candidates_split_queue(pkg, po, synth, pipeline):
     stats = assert_sequence_parity(po, ctx, ora, plan)
     assert sum(s[0] for s in stats.values()) == 0 and sum(s[2] for s in stats.values()) == 0, stats
     ctx.close()
+
+
+def test_streaming_sliding_window_with_slot_recycling(pkg, po, synth, pipeline):
+    """Live-SLAM order: key frames arrive one at a time, each searches the N key frames before it, the inter-KF
+    check follows once its neighbours have maps, and key frames that fell out of every window are released while
+    later work is still queued (sd_release_keyframe does not synchronise; their slots are recycled by the next
+    uploads).  Every checked key frame must equal the oracle run without any window."""
+    n, nkf = 4, 22
+    scene = synth.Scene(SMALL_CAM, seed=5)
+    images = {k: scene.render(k) for k in range(nkf)}
+    poses = {k: scene.pose(k) for k in range(nkf)}
+    nbrs = {k: np.arange(k - n, k, dtype=np.int32) for k in range(n, nkf)}
+    rots = {k: np.array([synth.Scene.rot_in_plane(k, int(j)) for j in nbrs[k]], np.float32) for k in nbrs}
+    prior = {k: pkg.stereo_search_constraints(scene.sparse_depths(k, 1000)) for k in nbrs}
+
+    ora = po.Oracle(threads=po.lib().ora_max_threads())
+    for k in range(nkf):
+        ora.add_keyframe(k, images[k], scene.K, poses[k])
+    for k in range(n, nkf):
+        ora.semidense(k, nbrs[k], rots[k], *prior[k])
+    checked = list(range(2 * n, nkf))
+    for k in checked:
+        ora.interkf(k, nbrs[k])
+        ora.pointset(k)
+
+    ctx = pkg.Context(0)
+    got = {}
+    for k in range(nkf):
+        ctx.upload_keyframe(k, images[k], scene.K, poses[k])
+        if k >= n:
+            ctx.semidense(k, nbrs[k], rots[k], *prior[k])
+        if k >= 2 * n:
+            ctx.interkf_check(k, nbrs[k])
+            ctx.update_pointset(k)
+            got[k] = ctx.download(k, points=True)          # synchronises on this key frame only
+            # key frame k - 2n is in no later window: neither as an image neighbour nor as a map neighbour
+            ctx.release_keyframe(k - 2 * n)
+    ctx.sync()
+    assert len(ctx_resident(ctx, range(nkf))) == 2 * n     # the window; everything older was recycled
+    for k in checked:
+        d, s, p = got[k]
+        assert np.array_equal(d, ora.plane(k, po.DEPTH_CHECKED)), f"depth kf {k}"
+        assert np.array_equal(s, ora.plane(k, po.SIGMA)), f"sigma kf {k}"
+        assert np.array_equal(p, ora.plane(k, po.POINTS)), f"points kf {k}"
+    assert sum(int((got[k][0] > 1e-6).sum()) for k in checked) > 1000
+    ctx.close()
+
+
+def ctx_resident(ctx, ids):
+    out = []
+    for k in ids:
+        try:
+            ctx.active_count(k)
+            out.append(k)
+        except Exception:
+            pass
+    return out
