@@ -36,7 +36,6 @@ struct Slot {
     uint32_t* list = nullptr;   // active pixels (k0_gradient), input of k1_search
     uint32_t* vlist = nullptr;  // pixels carrying a depth after the intra-KF stage (k23_intra), input of k4_inter_check
     KfMeta* meta = nullptr;
-    int* h_active = nullptr;    // pinned host copy of meta->active_count, valid once ev_up has completed
     bool vlist_ok = false;      // vlist / meta->valid_count describe `depth`
     bool has_semidense = false, has_checked = false, has_points = false, pose_changed = false;
     cudaEvent_t ev_up = nullptr;  // upload + K0 done (s_up)
@@ -93,7 +92,6 @@ struct sd_ctx {
     uint8_t* conf_out = nullptr;  // cap x (xyz, sigma, pixel)
     int conf_cap = 0;
     int* h_conf = nullptr;        // pinned: {total, confident}
-    int k1_tasks_per_warp = 0;      // > 0: k1_search warps retire after this many tasks (grid sized to the list), 0: persistent
 };
 
 namespace {
@@ -149,7 +147,6 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->list = (uint32_t*)p; p += lplane;
     s->vlist = (uint32_t*)p; p += lplane;
     s->meta = (KfMeta*)p;
-    if (cudaHostAlloc(&s->h_active, sizeof(int), cudaHostAllocDefault) != cudaSuccess) s->h_active = nullptr;
     cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_dn, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_sd, cudaEventDisableTiming);
@@ -162,7 +159,6 @@ void free_slot(Slot* s) {
     if (!s) return;
     cudaFree(s->slab);
     cudaFree(s->points);
-    if (s->h_active) cudaFreeHost(s->h_active);
     if (s->ev_up) cudaEventDestroy(s->ev_up);
     if (s->ev_dn) cudaEventDestroy(s->ev_dn);
     if (s->ev_sd) cudaEventDestroy(s->ev_sd);
@@ -280,8 +276,6 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
     k0_finalize<<<1, 1, 0, c->s_up>>>(s->meta, w, h);
     c->launches++;
     CU(c, cudaGetLastError());
-    // the list length travels to the host so that later launches over the list can be sized to it
-    if (s->h_active) CU(c, cudaMemcpyAsync(s->h_active, &s->meta->active_count, sizeof(int), cudaMemcpyDeviceToHost, c->s_up));
     CU(c, cudaEventRecord(s->ev_up, c->s_up));
     return SD_OK;
 }
@@ -310,7 +304,6 @@ void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
     A.task_counter = &s->meta->k1_task;
     A.hyp = nullptr; A.hyp_stride = 0;
     A.probe_out = nullptr;
-    A.max_tasks = 0xffffffffu;
 }
 
 void fill_nbr(Slot* s, Slot* nb, float rot, NbrConst& N) {
@@ -391,8 +384,6 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
         int use = per_sm;
         if (const char* e = getenv("SDPM_K1_BLOCKS_PER_SM")) use = std::max(1, std::min(per_sm, atoi(e)));
         c->k1_grid = c->sm_count * use;
-        c->k1_tasks_per_warp = K1_TASKS_PER_WARP_DEFAULT;
-        if (const char* e = getenv("SDPM_K1_TASKS_PER_WARP")) c->k1_tasks_per_warp = std::max(0, atoi(e));
         for (int i = 0; i < sd_ctx::RING; ++i)
             if (cudaEventCreateWithFlags(&c->ev_ring[i], cudaEventDisableTiming) != cudaSuccess) {
                 delete c;
@@ -507,19 +498,7 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     if (c->hypfree_valid[hb]) CU(c, cudaStreamWaitEvent(c->s_srch, c->ev_hypfree[hb], 0));
     CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), c->s_srch));
     {
-        // Blocks that retire after a bounded number of tasks let the high-priority kernels of the previous key
-        // frames (s_main, s_chk) onto the SMs while the search is still running; the grid covers the list
-        // length when the host already knows it (K0 finished), else the list's capacity.
-        int grid = c->k1_grid;
-        A.max_tasks = 0xffffffffu;
-        if (c->k1_tasks_per_warp > 0) {
-            long long cap = (long long)(c->W - 2 * c->P.border) * (c->H - 2 * c->P.border);
-            if (s->h_active && cudaEventQuery(s->ev_up) == cudaSuccess) cap = std::max(0, *s->h_active);
-            const long long ntask = ((cap + 31) / 32) * n;
-            const long long per_block = (long long)K1_WARPS * c->k1_tasks_per_warp;
-            grid = (int)std::max(1ll, (ntask + per_block - 1) / per_block);
-            A.max_tasks = (unsigned)c->k1_tasks_per_warp;
-        }
+        const int grid = c->k1_grid;
         ScopedTimer t(c, c->s_srch, T_SEARCH);
         k1_search<<<grid, K1_WARPS * 32, 0, c->s_srch>>>(A);
     }

@@ -66,7 +66,6 @@ struct SearchArgs {
     const KfMeta* meta;
     int count_override;  // >= 0: use instead of meta->active_count (probes)
     unsigned int* task_counter;  // zeroed before the launch; warps draw 32-entry tasks from it
-    unsigned int max_tasks;      // a warp retires after this many tasks (0xffffffff: persistent warps)
     float2* hyp;       // nullable; hypothesis buffer [neighbour][hyp_stride]: (rho, sigma), or (-1, 0) for none
     int hyp_stride;
     float* probe_out;  // nullable; [entry][6] = {rho, sigma, best uj, supported, best_u, best_v} of neighbour 0
@@ -499,10 +498,7 @@ constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller st
 #define K4_MIN_BLOCKS 8
 #endif
 #ifndef K1_MIN_BLOCKS
-#define K1_MIN_BLOCKS 5
-#endif
-#ifndef K1_TASKS_PER_WARP_DEFAULT
-#define K1_TASKS_PER_WARP_DEFAULT 0
+#define K1_MIN_BLOCKS 6
 #endif
 #define K1_TIE_REL 2e-6f            // float shortcut of err: two candidates closer than this are re-scanned exactly
 #define K1_ERR_LIMIT_LO 999000.0f   // PM.cc:437 initial best_match_err = 1e6
@@ -531,6 +527,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     __shared__ uint32_t s_beste[K1_WARPS][32];
     __shared__ uint32_t s_bestu[K1_WARPS][32];
     __shared__ uint32_t s_tie[K1_WARPS][32];  // per owner lane: two best errs too close for the float shortcut
+    __shared__ uint32_t s_rng[K1_WARPS][32];  // per lane: u_lo | (u_hi + 1) << 16 -- parked for phase (D), which is register-lean
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
@@ -552,12 +549,12 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
   // planes of one or two neighbour key frames (L2-resident), and a task is short enough (~1/10 of a
   // pixel's work) that the last warps to finish do not leave the machine idle for long.
   const unsigned nblk = ((unsigned)count + 31u) >> 5;
-  const unsigned long long ntask = (unsigned long long)nblk * (unsigned)A.n;
-  for (unsigned drawn = 0; drawn < A.max_tasks; ++drawn) {
+  const unsigned ntask = nblk * (unsigned)A.n;  // < 2^31: planes hold < 2^30 pixels (checked at upload), n <= 40
+  for (;;) {
     unsigned task = 0;
     if (lane == 0) task = atomicAdd(A.task_counter, 1u);
     task = __shfl_sync(full, task, 0);
-    if ((unsigned long long)task >= ntask) break;
+    if (task >= ntask) break;
     const int j = (int)(task / nblk);
     const int entry = (int)(task - (unsigned)j * nblk) * 32 + lane;
     const bool valid = entry < count;
@@ -573,7 +570,6 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     const float g1 = valid ? __ldg(A.grad + (size_t)y * A.pitch_f + x) : 0.f;         // PM.cc:434
     const float th1 = valid ? __ldg(A.theta + (size_t)y * A.pitch_f + x) : 0.f;       // PM.cc:214
     const float xp0 = (xf - A.cx) / A.fx, xp1 = (yf - A.cy) / A.fy;                   // PM.cc:893, 862
-    const double xp0d = (double)xp0, xp1d = (double)xp1;
 
     {
         const NbrConst& N = A.nb[j];
@@ -630,6 +626,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
 
         par4[lane] = make_float4(ab, cb, I1, g1);
         par2[lane] = make_float2(th_epi, apr);
+        s_rng[wib][lane] = (uint32_t)(u_lo & 0xffff) | ((uint32_t)(u_hi + 1) << 16);  // 0 <= u_lo <= W, -1 <= u_hi <= W
         beste[lane] = 0x7f800000u;  // +inf
         tie[lane] = 0;
         __syncwarp();
@@ -774,10 +771,17 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         __syncwarp();
 
         // ---------------- (D) refinement + hypothesis: PM.cc:446-463, 806-829 ----------------
+        // everything phase (D) needs was parked in shared memory by phase (A): the scan and the evaluation above run
+        // with few live registers (6 resident blocks per SM), and (D) reloads instead of keeping values alive
+        const float4 own4 = par4[lane];
+        const float abD = own4.x, cbD = own4.y, I1D = own4.z, g1D = own4.w;
         int bj = -1;
         if (tie[lane]) {
+            const float2 own2 = par2[lane];
+            const uint32_t rg = s_rng[wib][lane];
             LineScan L;
-            L.ab = ab; L.cb = cb; L.I1 = I1; L.g1 = g1; L.th_epi = th_epi; L.apr = apr; L.u_lo = u_lo; L.u_hi = u_hi;
+            L.ab = abD; L.cb = cbD; L.I1 = I1D; L.g1 = g1D; L.th_epi = own2.x; L.apr = own2.y;
+            L.u_lo = (int)(rg & 0xffffu); L.u_hi = (int)(rg >> 16) - 1;
             bj = exact_line_scan(A, N, L);
         } else if (beste[lane] != 0x7f800000u) {
             bj = (int)bestu[lane];
@@ -786,11 +790,11 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         float best_u = 0.f;
         const bool found = bj >= 0;
         if (found) {
-            const float yb = -(ab * (float)bj + cb);
-            const float rI = I1 - bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yb, bj);
-            const float rG = g1 - bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yb, bj);
+            const float yb = -(abD * (float)bj + cbD);
+            const float rI = I1D - bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yb, bj);
+            const float rG = g1D - bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yb, bj);
             const int up = bj + 1, um = bj - 1;
-            const float yp = -(ab * (float)up + cb), ym = -(ab * (float)um + cb);
+            const float yp = -(abD * (float)up + cbD), ym = -(abD * (float)um + cbD);
             const float g = (bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yp, up) -
                              bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, ym, um)) / 2;
             const float q = (bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yp, up) -
@@ -801,7 +805,10 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
             best_u = ustar;  // PM.cc:459
             const float istd = N.meta->istddev;
             const float uvar = 2 * istd * istd / den;  // PM.cc:457
-            // ComputeInvDepthHypothesis
+            // ComputeInvDepthHypothesis (xp recomputed from the list entry with the arithmetic of phase (A))
+            const uint32_t ent = A.list[entry];
+            const double xp0d = (double)(((float)(int)(ent & 0xffffu) - A.cx) / A.fx);
+            const double xp1d = (double)(((float)(int)(ent >> 16) - A.cy) / A.fy);
             const double d2 = N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d);
             const double d0 = N.Rd0[2] + __fma_rn(N.Rd0[1], xp1d, N.Rd0[0] * xp0d);
             const float num2f = (float)(d0 * (double)A.fx);
@@ -818,7 +825,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
             if (A.probe_out && j == 0) {
                 float* o = A.probe_out + (size_t)entry * 6;
                 o[0] = found ? rho : 0.f; o[1] = sig; o[2] = (float)bj; o[3] = found ? 1.f : 0.f;
-                o[4] = best_u; o[5] = found ? -(ab * best_u + cb) : 0.f;  // PM.cc:459-460
+                o[4] = best_u; o[5] = found ? -(abD * best_u + cbD) : 0.f;  // PM.cc:459-460
             }
         }
         __syncwarp();
