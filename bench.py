@@ -20,6 +20,11 @@ Timing: CUDA events over all of the context's streams (sd_span_begin/end), barri
 torch.cuda.synchronize() on both sides, max over ranks.  L2: the working set per step (~5 GB)
 is far larger than the 126 MB L2, so no explicit flush is needed ("inputs_larger_than_l2").
 
+`roofline` is quoted on stage K1 (k1_search + k1_fuse): `avg_launch_us` comes from the events of the timed region,
+where the context's streams overlap on purpose (a kernel's events then also span the time it shares the SMs with
+kernels of other key frames); `standalone_launch_us` / `kernels_standalone_us` come from one extra untimed pass with
+every stream drained before each kernel -- those are the durations the ncu launch list (profiles/) agrees with.
+
 --impl reference times the reference's CPU algorithm for the path (the oracle port, all host
 threads) on a bounded sample of the same workload; rank 0 only.
 """
@@ -337,6 +342,16 @@ def run_b200(args):
     ctx.timing_enable(False)
     ms_e, _, _ = timed(True, args.steps, max(args.warmup, 1))
 
+    # standalone kernel durations: one more untimed pass with every stream drained before each kernel, so a launch's
+    # events bracket that kernel alone.  In the timed region the five streams overlap on purpose; there the events
+    # of a kernel also span the time it shares the SMs with (or waits behind) kernels of other key frames.
+    ctx.timing_enable(True, serial=True)
+    ctx.timing_reset()
+    step(False)
+    ctx.sync()
+    kt_alone = ctx.timing()
+    ctx.timing_enable(False)
+
     kf_total_per_step = args.nkf * world
     value = kf_total_per_step * args.steps / (ms_v * 1e-3)
     e2e = kf_total_per_step * args.steps / (ms_e * 1e-3)
@@ -353,6 +368,8 @@ def run_b200(args):
         k1_ms += kt["fuse"][0]
         k1_avg_s = (k1_ms / max(k1_n, 1)) * 1e-3
         achieved = bpp["search"] * px / k1_avg_s / 1e9 if k1_avg_s > 0 else 0.0
+        alone_us = {k: (v[0] / max(v[1], 1)) * 1e3 for k, v in kt_alone.items()}
+        k1_alone_s = (alone_us["search"] + alone_us["fuse"]) * 1e-6
         traffic = None
         try:
             with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
@@ -377,8 +394,12 @@ def run_b200(args):
                          "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "algorithmic_bytes_per_launch": bpp["search"] * px,
                          "avg_launch_us": k1_avg_s * 1e6,
+                         "standalone_launch_us": k1_alone_s * 1e6,
+                         "standalone_achieved": bpp["search"] * px / k1_alone_s / 1e9 if k1_alone_s > 0 else 0.0,
                          "whole_path_frac": sum(bpp.values()) * px * (value / world) / 1e9 / peak},
             "kernels_avg_us": {k: (v[0] / max(v[1], 1)) * 1e3 for k, v in kt.items()},
+            "kernels_standalone_us": alone_us,
+            "kernels_standalone_share": {k: v / max(sum(alone_us.values()), 1e-9) for k, v in alone_us.items()},
             "valid_fraction": valid_fraction,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -143,7 +143,9 @@ int sd_launch_count(sd_ctx* ctx, uint64_t* out);
  * end = join the streams, record an event, wait, return the elapsed milliseconds (CUDA events). */
 int sd_span_begin(sd_ctx* ctx);
 int sd_span_end(sd_ctx* ctx, double* ms);
-/* Per-kernel device timing (CUDA events on the launching stream). enable=1 starts collecting. */
+/* Per-kernel device timing (CUDA events on the launching stream). enable=1 starts collecting; enable=2 also drains every
+ * stream before each timed kernel, so that the durations are those of the kernel running alone (diagnostic: it
+ * serialises the pipeline). */
 int sd_timing_enable(sd_ctx* ctx, int enable);
 /* names: "grad", "search", "fuse", "intra" (checking + growing, one kernel), "inter", "points"; returns accumulated ms and launches */
 int sd_timing_get(sd_ctx* ctx, const char* name, double* ms, uint64_t* launches);

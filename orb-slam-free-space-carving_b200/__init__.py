@@ -295,8 +295,8 @@ class Context:
         self._ck(self.L.sd_span_end(self.h, C.byref(ms)))
         return ms.value
 
-    def timing_enable(self, on=True):
-        self._ck(self.L.sd_timing_enable(self.h, 1 if on else 0))
+    def timing_enable(self, on=True, serial=False):
+        self._ck(self.L.sd_timing_enable(self.h, (2 if serial else 1) if on else 0))
 
     def timing_reset(self):
         self._ck(self.L.sd_timing_reset(self.h))

@@ -79,6 +79,7 @@ struct sd_ctx {
     std::string err;
     uint64_t launches = 0;
     bool timing = false;
+    bool timing_serial = false;  // sd_timing_enable(ctx, 2): every timed kernel runs alone (streams drained before it)
     std::vector<TimedSpan> spans;
     std::vector<cudaEvent_t> ev_pool;
     double t_ms[T_COUNT] = {0};
@@ -184,6 +185,13 @@ struct ScopedTimer {  // CUDA events on the launching stream around one kernel
     cudaEvent_t a = nullptr, b = nullptr;
     ScopedTimer(sd_ctx* c_, cudaStream_t s_, int w) : c(c_), s(s_), which(w) {
         if (c->timing) {
+            if (c->timing_serial) {  // standalone durations: nothing else may be running while this kernel does
+                cudaStreamSynchronize(c->s_up);
+                cudaStreamSynchronize(c->s_srch);
+                cudaStreamSynchronize(c->s_main);
+                cudaStreamSynchronize(c->s_chk);
+                cudaStreamSynchronize(c->s_dn);
+            }
             a = pool_event(c);
             b = pool_event(c);
             cudaEventRecord(a, s);
@@ -913,6 +921,7 @@ int sd_span_end(sd_ctx* c, double* ms) {
 int sd_timing_enable(sd_ctx* c, int enable) {
     if (!c) return SD_ERR_INVALID_ARG;
     c->timing = enable != 0;
+    c->timing_serial = enable == 2;
     return SD_OK;
 }
 
