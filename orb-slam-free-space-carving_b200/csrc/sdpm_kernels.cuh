@@ -1124,8 +1124,7 @@ __global__ void __launch_bounds__(256) k_build_vlist(const float* __restrict__ d
 struct K4Proj {  // projection of one pixel into one neighbour + the four depth taps, PM.cc:675-705
     bool inb;
     float rz, depthj;
-    const float* spl;
-    float d[4];
+    float d[4], s[4];
 };
 
 __device__ __forceinline__ void k4_project(const InterArgs& A, const InterNbr& N, float xp0, float xp1, double xp0d, double xp1d,
@@ -1146,17 +1145,23 @@ __device__ __forceinline__ void k4_project(const InterArgs& A, const InterNbr& N
     // Eq. 12, PM.cc:684-688
     P.rz = (float)(N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d));
     P.depthj = depthp / (P.rz + depthp * N.t[2]);
-    P.spl = N.sigma;
     P.d[0] = P.d[1] = P.d[2] = P.d[3] = 0.f;
+    P.s[0] = P.s[1] = P.s[2] = P.s[3] = 0.f;
     if (P.inb) {
         const int x0 = (int)xj, y0 = (int)yj;  // floor of a non-negative float
         const size_t q = (size_t)y0 * A.pitch_f + x0;
         const float* dpl = N.depth + q;
-        P.spl = N.sigma + q;
+        const float* spl = N.sigma + q;
         P.d[0] = __ldg(dpl);                  // taps (y0,x0) (y1,x0) (y0,x1) (y1,x1), PM.cc:705-752
         P.d[1] = __ldg(dpl + A.pitch_f);
         P.d[2] = __ldg(dpl + 1);
         P.d[3] = __ldg(dpl + A.pitch_f + 1);
+        // the sigma taps are requested with the depth taps, not after them: a load that waits for `d > 1e-6` is a
+        // second dependent trip to L2 per neighbour, and this kernel is bound by exactly that latency
+        P.s[0] = __ldg(spl);
+        P.s[1] = __ldg(spl + A.pitch_f);
+        P.s[2] = __ldg(spl + 1);
+        P.s[3] = __ldg(spl + A.pitch_f + 1);
     }
 }
 
@@ -1187,7 +1192,7 @@ __global__ void __launch_bounds__(128, K4_MIN_BLOCKS) k4_inter_check(const __gri
             for (int t = 0; t < 4; ++t) {
                 const float d = cur.d[t];
                 if (d > SD_EPS_F) {
-                    const float s = __ldg(cur.spl + (t & 1) * A.pitch_f + (t >> 1));
+                    const float s = cur.s[t];
                     const float dl = cur.depthj - d;
                     const float nf = dl * dl, qf = s * s;
                     const float est = __fdividef(nf, qf);
