@@ -237,22 +237,24 @@ __global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __res
         }
     }
 
-    // 128 pixels x 32 planes -> 32 planes x 4 words: the warp (one image row of the tile) transposes
-    // its membership words with ballots; lane s ends up with the 4 words of plane s.
+    // 128 pixels x 32 planes -> 32 planes x 4 words: the warp (one image row of the tile) transposes four 32x32 bit
+    // matrices (rows = columns of the image, held one per lane; bits = planes) with the five-stage butterfly --
+    // lanes i and i^j swap their off-diagonal j x j blocks -- so that lane s ends up with the word of plane s.
     __syncwarp();
     const unsigned full = 0xffffffffu;
     uint32_t pw[K0_PX], pall[K0_PX];
 #pragma unroll
     for (int w = 0; w < K0_PX; ++w) {
-        const uint32_t v = s_memb[ty][w * 32 + tx];
-        uint32_t mine = 0;
-#pragma unroll
-        for (int s = 0; s < SD_ARC_CELLS; ++s) {
-            const uint32_t b = __ballot_sync(full, (v >> s) & 1u);
-            if (tx == s) mine = b;
-        }
-        pw[w] = mine;
+        uint32_t v = s_memb[ty][w * 32 + tx];
         pall[w] = __ballot_sync(full, v != 0u);
+        uint32_t m = 0x0000ffffu;
+#pragma unroll
+        for (int j = 16; j; j >>= 1) {
+            const uint32_t other = __shfl_xor_sync(full, v, j);
+            v = (tx & j) ? ((v & ~m) | ((other >> j) & m)) : ((v & m) | ((other << j) & ~m));
+            m ^= m << (j >> 1);
+        }
+        pw[w] = v;
     }
     if (y < H) {  // arc_pitch is a multiple of 4 words and covers the last tile: aligned uint4 stores
         const size_t plane = (size_t)H * arc_pitch;
