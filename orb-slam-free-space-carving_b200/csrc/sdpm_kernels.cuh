@@ -167,7 +167,7 @@ constexpr int SD_ARC_PLANES = SD_ARC_CELLS + 1;
 #define SD_ARC_CELL_DEG 11.25f
 #define SD_ARC_MARGIN 0.05f
 
-__global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __restrict__ img, int pitch_u8, int W, int H,
+__global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __restrict__ img, int pitch_u8, int W, int H,
                                                             float* __restrict__ grad, float* __restrict__ theta, int pitch_f,
                                                             uint32_t* __restrict__ arc, int arc_pitch,
                                                             uint32_t* __restrict__ list, KfMeta* __restrict__ meta,
@@ -182,10 +182,28 @@ __global__ void __launch_bounds__(K0_TX* K0_TY) k0_gradient(const uint8_t* __res
     const int tid = ty * K0_TX + tx;
     const int x0 = blockIdx.x * K0_TW, y0 = blockIdx.y * K0_TY;
 
-    for (int i = tid; i < (K0_TY + 2) * (K0_TW + 2); i += K0_TX * K0_TY) {
-        int r = i / (K0_TW + 2), c = i - r * (K0_TW + 2);
-        int yy = clampi(y0 - 1 + r, 0, H - 1), xx = clampi(x0 - 1 + c, 0, W - 1);
-        tile[r][c] = __ldg(img + (size_t)yy * pitch_u8 + xx);
+    if (x0 + K0_TW < W) {
+        // interior columns: the 128 tile bytes of a row are 32 aligned words (x0 and the pitch are multiples of 128),
+        // plus one halo byte on each side; rows clamp to the image (replicate border)
+        for (int i = tid; i < (K0_TY + 2) * 34; i += K0_TX * K0_TY) {
+            const int r = i / 34, k = i - r * 34;
+            const uint8_t* row = img + (size_t)clampi(y0 - 1 + r, 0, H - 1) * pitch_u8;
+            if (k < 32) {
+                const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(row + x0) + k);
+                uint8_t* d = &tile[r][1 + 4 * k];  // tile column c <-> x0 - 1 + c: byte-wise stores (1 + 4k is not word-aligned)
+                d[0] = (uint8_t)v; d[1] = (uint8_t)(v >> 8); d[2] = (uint8_t)(v >> 16); d[3] = (uint8_t)(v >> 24);
+            } else if (k == 32) {
+                tile[r][0] = __ldg(row + max(x0 - 1, 0));
+            } else {
+                tile[r][K0_TW + 1] = __ldg(row + x0 + K0_TW);  // < W here
+            }
+        }
+    } else {
+        for (int i = tid; i < (K0_TY + 2) * (K0_TW + 2); i += K0_TX * K0_TY) {
+            int r = i / (K0_TW + 2), c = i - r * (K0_TW + 2);
+            int yy = clampi(y0 - 1 + r, 0, H - 1), xx = clampi(x0 - 1 + c, 0, W - 1);
+            tile[r][c] = __ldg(img + (size_t)yy * pitch_u8 + xx);
+        }
     }
     __syncthreads();
 
