@@ -442,7 +442,7 @@ __device__ __forceinline__ bool chi_test_q(float a, float b, float qa, float qb,
     const float dl = a - b;
     const float num = dl * dl;
     const float approx = num * ra + num * rb;
-    if (fminf(qa, qb) > 1e-30f) {  // reciprocals of tinier squares overflow: the estimate would not track the quotient
+    if (fminf(qa, qb) > 1e-30f && fmaxf(qa, qb) < 1e30f) {  // outside, the (approximate) reciprocals over/underflow: the estimate would not track the quotient
         if (approx < thr_lo) return true;
         if (approx > thr_hi) return false;
     }
@@ -465,7 +465,7 @@ __device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const flo
     for (int i = 0; i < NT; ++i) {
         const float q = hs[i] * hs[i];
         hq[i] = q;
-        hr[i] = 1.0f / q;
+        hr[i] = __fdividef(1.0f, q);  // only steers the division-free estimate of chi_test_q (error ~2e-7 << its 1e-5 guard band)
         // ChiTest(a, a): num = +0, chi = 0/q + 0/q = 0 unless q is 0 or NaN (then NaN -> false)
         cnt[i] = (q > 0.0f && 0.0f < thr) ? 1 : 0;
     }
@@ -879,7 +879,9 @@ __global__ void __launch_bounds__(128, K1F_MIN_BLOCKS) k1_fuse(const FuseArgs F)
         if (j < F.n) {
             const float2 h = __ldg(F.hyp + (size_t)j * F.hyp_stride + e);
             hd[j] = h.x; hs[j] = h.y;
-            if (1 / h.x > 0.0f) { present |= 1ull << j; ++nh; }
+            // PM.cc:216 keeps a hypothesis if `1 / depth > 0`: true exactly for +0 and the positive finite floats
+            // (1/+0 = +inf, 1/+inf = 0, NaN compares false), i.e. for bit patterns below +inf -- no division needed
+            if (__float_as_uint(h.x) < 0x7f800000u) { present |= 1ull << j; ++nh; }
         }
     }
     if (nh > F.lambdaN) {
@@ -991,7 +993,7 @@ __global__ void __launch_bounds__(K23_THREADS) k23_intra(const IntraArgs A) {
             const double sq = (double)s * (double)s;  // pow(sigma, 2)
             s_r[i] = 1.0 / sq;
             s_dq[i] = (double)d / sq;
-            s_rq[i] = 1.0f / (s * s);
+            s_rq[i] = __fdividef(1.0f, s * s);  // steers chi_test_q only
         }
         __syncthreads();
         // ---- checking stage over the list (tile + 1-pixel halo, image interior only) ----
