@@ -180,6 +180,33 @@ def run_reference(args):
 # ------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------
+def bind_to_gpu_numa_node(torch, local):
+    """One process per GPU on a multi-socket box: run the rank (and first-touch its pinned staging buffers) on the
+    CPUs of the GPU's own NUMA node, so that the host<->device copies of the e2e leg do not cross the socket link.
+    Best effort: returns the cpu list string it bound to, or None."""
+    try:
+        pr = torch.cuda.get_device_properties(local)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        path = "/sys/bus/pci/devices/%s/local_cpulist" % bus.lower()
+        with open(path) as f:
+            cpulist = f.read().strip()
+        cpus = set()
+        for part in cpulist.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if len(cpus) >= 2:
+            os.sched_setaffinity(0, cpus)
+            return cpulist
+    except Exception:
+        pass
+    return None
+
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -192,6 +219,7 @@ def run_b200(args):
         dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_numa_node(torch, local) if world > 1 else None   # before any pinned allocation (first touch)
 
     pkg = load_package()
     synth = importlib.import_module(PKG_NAME + ".synth")
@@ -330,7 +358,7 @@ def run_b200(args):
         launches = ctx.launch_count() - l0
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         if os.environ.get("BENCH_VERBOSE"):
-            sys.stderr.write(f"rank {rank}: span {ms:.2f} ms for {steps} steps, host issue {host_issue_ms[-1]:.2f} ms\n")
+            sys.stderr.write(f"rank {rank}: numa cpus {numa}; span {ms:.2f} ms for {steps} steps, host issue {host_issue_ms[-1]:.2f} ms\n")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, clocks
