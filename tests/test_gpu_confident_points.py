@@ -85,6 +85,10 @@ def test_confident_points_ties_and_odd_values(pkg, po, w, h):
     ctx.import_maps(0, dd.data_ptr(), ss.data_ptr())
     ctx.sync()
     ora.set_maps(0, depth, sigma)
+    # K5 on the same crafted map: widths that are not a multiple of 4 take the scalar store path of k5_pointset
+    ctx.update_pointset(0)
+    ora.pointset(0)
+    assert np.array_equal(ctx.plane(0, po.POINTS).view(np.uint32), ora.plane(0, po.POINTS).view(np.uint32))
     for max_sigma in (0.01, 0.0125, 1e30):
         full = ora.confident_points(0, max_sigma, 0)
         _same(ctx.confident_points(0, max_sigma, 0), full, f"max_sigma {max_sigma} all")
