@@ -532,7 +532,10 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         if (n <= 6) k1_fuse<6><<<blocks, 128, 0, c->s_main>>>(F);
         else if (n <= 10) k1_fuse<10><<<blocks, 128, 0, c->s_main>>>(F);
         else if (n <= 16) k1_fuse<16><<<blocks, 128, 0, c->s_main>>>(F);
-        else k1_fuse<SD_MAX_NEIGHBOURS><<<blocks, 128, 0, c->s_main>>>(F);
+        else {
+            const int cap = (c->W - 2 * c->P.border) * (c->H - 2 * c->P.border);
+            k1_fuse_rows<<<(cap + K1FR_THREADS - 1) / K1FR_THREADS, K1FR_THREADS, k1fr_smem_bytes(n), c->s_main>>>(F);
+        }
     }
     CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
     c->hypfree_valid[hb] = true;

@@ -895,6 +895,73 @@ __global__ void __launch_bounds__(128, K1F_MIN_BLOCKS) k1_fuse(const FuseArgs F)
     }
 }
 
+// k1_fuse for many neighbours (n > 16): the register-array version above would need > 128 registers (or local
+// memory: 287 us at n = 20, 1 031 us at n = 40).  Here a thread keeps its pixel's hypotheses and their compatibility
+// counts in its own column of shared memory and walks the ChiTests row by row: the row's values and its count live in
+// registers, the partner's q = sigma^2 and its reciprocal estimate are recomputed (one FMUL + one MUFU) instead of
+// stored, each unordered pair is tested once (ChiTest is symmetric) and credits the partner's count in shared memory.
+// Rows are visited in ascending order, so a row's count is complete when the row is reached: "first largest set"
+// (PM.cc:616) is decided on the fly.  No __syncthreads: a thread only ever touches its own column.
+constexpr int K1FR_THREADS = 64;
+__host__ __device__ constexpr size_t k1fr_smem_bytes(int n) { return (size_t)n * K1FR_THREADS * (2 * sizeof(float) + 1); }
+
+__global__ void __launch_bounds__(K1FR_THREADS) k1_fuse_rows(const FuseArgs F) {
+    extern __shared__ float k1fr_smem[];
+    const int T = K1FR_THREADS, tid = threadIdx.x, n = F.n;
+    float* sd = k1fr_smem + tid;                                                 // sd[j * T]: inverse depth of hypothesis j
+    float* ss = k1fr_smem + n * T + tid;                                         // ss[j * T]: sigma
+    unsigned char* sc = reinterpret_cast<unsigned char*>(k1fr_smem + 2 * n * T) + tid;  // sc[j * T]: compatible hypotheses so far
+    const int e = blockIdx.x * T + tid;
+    if (e >= F.meta->active_count) return;
+    const float thr = F.chi_fuse, thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
+    unsigned long long present = 0;
+    int nh = 0;
+    for (int j = 0; j < n; ++j) {
+        const float2 h = __ldg(F.hyp + (size_t)j * F.hyp_stride + e);
+        sd[j * T] = h.x;
+        ss[j * T] = h.y;
+        sc[j * T] = (h.y * h.y > 0.0f && 0.0f < thr) ? 1 : 0;                    // ChiTest(a, a), see fuse_hypotheses
+        if (__float_as_uint(h.x) < 0x7f800000u) { present |= 1ull << j; ++nh; }  // PM.cc:216, see k1_fuse
+    }
+    if (nh <= F.lambdaN) return;  // PM.cc:221
+    int best_cnt = 0, best_a = -1;
+    for (unsigned long long mi = present; mi; mi &= mi - 1) {
+        const int i = __ffsll((long long)mi) - 1;
+        const float di = sd[i * T], si = ss[i * T];
+        const float qi = si * si, ri = __fdividef(1.0f, qi);
+        int c = sc[i * T];
+        for (unsigned long long mk = mi & (mi - 1); mk; mk &= mk - 1) {  // present hypotheses after i
+            const int k = __ffsll((long long)mk) - 1;
+            const float sk = ss[k * T];
+            const float qk = sk * sk;
+            if (chi_test_q(di, sd[k * T], qi, qk, ri, __fdividef(1.0f, qk), thr, thr_lo, thr_hi)) {
+                ++c;
+                ++sc[k * T];
+            }
+        }
+        if (c > best_cnt) { best_cnt = c; best_a = i; }  // strict >, first largest set wins (PM.cc:616)
+    }
+    if (best_cnt < F.lambdaN) return;  // PM.cc:623: unsupported
+    const float da = sd[best_a * T], sa = ss[best_a * T];
+    const float qa = sa * sa, ra = __fdividef(1.0f, qa);
+    // GetFusion(depthHo), PM.cc:947-970: pow(sigma,2) in double, float accumulators, members in index order
+    float pjsj = 0, rsj = 0;
+    for (unsigned long long mb = present; mb; mb &= mb - 1) {
+        const int ib = __ffsll((long long)mb) - 1;
+        const float db = sd[ib * T], sb = ss[ib * T];
+        const float qb = sb * sb;
+        const bool comp = (ib == best_a) ? (qa > 0.0f && 0.0f < thr) : chi_test_q(da, db, qa, qb, ra, __fdividef(1.0f, qb), thr, thr_lo, thr_hi);
+        if (!comp) continue;
+        const double s2 = (double)sb * (double)sb;
+        pjsj = (float)((double)pjsj + (double)db / s2);
+        rsj = (float)((double)rsj + 1.0 / s2);
+    }
+    const uint32_t ent = F.list[e];
+    const size_t o = (size_t)(ent >> 16) * F.pitch_f + (ent & 0xffffu);
+    F.depth[o] = pjsj / rsj;
+    F.sigma[o] = sqrtf(1 / rsj);
+}
+
 // fusion probe: one thread, same device function as k1_fuse
 __global__ void k1_fusion_probe(const float* d, const float* s, int n, int lambdaN, float chi_fuse, float* out) {
     float hd[SD_MAX_NEIGHBOURS], hs[SD_MAX_NEIGHBOURS];

@@ -71,6 +71,18 @@ def test_max_neighbours_n40_and_wide_prior(pkg, po, synth, pipeline):
     ctx.close()
 
 
+def test_n20_config3_neighbourhood(pkg, po, synth, pipeline):
+    """BASELINE.json configs[2] neighbourhood (20 covisible neighbours): the shared-memory row version of the
+    hypothesis fusion (k1_fuse_rows, n > 16)."""
+    scene, plan, images = _setup(synth, pipeline, SMALL_CAM, 24, 20, seed=19)
+    ora = run_oracle(po, plan, images)
+    ctx = run_gpu(pkg, pipeline, plan, images)
+    stats = assert_sequence_parity(po, ctx, ora, plan)
+    assert sum(s[2] for s in stats.values()) == 0, f"differing values {stats}"     # measured: bit-exact
+    assert (ctx.plane(plan.ids[12], po.DEPTH_CHECKED) > 1e-6).mean() > 0.05
+    ctx.close()
+
+
 def test_1080p_n5(pkg, po, synth, pipeline):
     scene, plan, images = _setup(synth, pipeline, "1080p", 6, 5, seed=3)
     ora = run_oracle(po, plan, images)
