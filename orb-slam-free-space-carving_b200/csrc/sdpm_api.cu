@@ -229,7 +229,8 @@ void set_pose_fields(Slot* s, const float Tcw[12]) {
 
 int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int w, int h, int stride, const float K[4],
                   const float Tcw[12]) {
-    if (!c || !gray || !K || !Tcw || w < 8 || h < 8 || stride < w || w > 65535 || h > 65535 ||
+    if (!c || !gray || !K || !Tcw || w < 8 || h < 8 || stride < w ||
+        w > 65534 || h > 65535 ||                  // list entries pack (y, x) in 16 bits each; k1_search packs u_hi + 1 <= w + 1
         (long long)(w + 128) * h >= (1ll << 30))  // kernels index planes with 32-bit element offsets
         return fail(c, SD_ERR_INVALID_ARG, "sd_upload_keyframe: bad argument");
     CU(c, cudaSetDevice(c->device));
