@@ -426,3 +426,35 @@ def ctx_resident(ctx, ids):
         except Exception:
             pass
     return out
+
+
+def test_per_keyframe_intrinsics(pkg, po, synth, pipeline):
+    """Every key frame carries its own K (PM.cc reads kf->fx.. of key frame 1 in GetSearchRange / GetPixelDepth,
+    K1 and K2 in ComputeFundamental, Kj of the neighbour in InterKeyFrameDepthChecking): perturbed intrinsics per
+    key frame, same values on both sides -- physically off, but every formula must still agree bit for bit."""
+    scene, plan, images = _setup(synth, pipeline, SMALL_CAM, 9, 6, seed=23)
+    Ks = {}
+    for k in plan.ids:
+        K = np.array(scene.K, np.float32).copy()
+        K[0] *= np.float32(1.0 + 0.01 * np.sin(1.3 * k))
+        K[1] *= np.float32(1.0 - 0.008 * np.cos(0.7 * k))
+        K[2] += np.float32(0.9 * np.sin(k))
+        K[3] -= np.float32(0.6 * np.cos(2 * k))
+        Ks[k] = K
+    ora = po.Oracle(threads=po.lib().ora_max_threads())
+    ctx = pkg.Context(0)
+    for k in plan.ids:
+        ora.add_keyframe(k, images[k], Ks[k], plan.poses[k])
+        ctx.upload_keyframe(k, images[k], Ks[k], plan.poses[k])
+    for k in plan.ids:
+        ora.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
+    for k in plan.ids:
+        ora.interkf(k, plan.nbrs[k])
+        ora.pointset(k)
+    pipeline.semidense_all(ctx, plan)
+    pipeline.interkf_all(ctx, plan)
+    ctx.sync()
+    stats = assert_sequence_parity(po, ctx, ora, plan)
+    assert sum(s[2] for s in stats.values()) == 0, f"differing values {stats}"
+    assert sum(int((ctx.plane(k, po.DEPTH) > 1e-6).sum()) for k in plan.ids) > 1000
+    ctx.close()
