@@ -551,7 +551,6 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
-    const unsigned lt_mask = (1u << lane) - 1u;
     const int count = A.count_override >= 0 ? A.count_override : A.meta->active_count;
 
     uint32_t* queue = s_queue[wib];
