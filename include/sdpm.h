@@ -46,7 +46,13 @@ typedef struct SdParams {
     double chi2_fuse;  /* 5.99, PM.cc:917, 923                                                    */
     double chi2_inter; /* 3.84, PM.cc:710                                                         */
     float slope_limit; /* 4,    PM.cc:393                                                         */
-    int border;        /* 2,    PM.cc:198-199                                                     */
+    int border;        /* 2,    PM.cc:198-199, 492, 555, 659: must be 2 (hard-coded in every reference loop) */
+    int interkf_inplace; /* 0 (default): InterKeyFrameDepthChecking reads its neighbours' maps as they were after the
+                          * intra-key-frame stage (snapshot, order-independent, what multi-GPU runs need).
+                          * 1: the reference's in-place behaviour (PM.cc:764, 793 overwrite depth_map_ inside the loop over
+                          * key frames, PM.cc:262-307): a neighbour that has already been checked is read as checked, so
+                          * the result depends on the order of the sd_interkf_check calls, as the reference's depends on
+                          * its visiting order.  Single GPU only. */
 } SdParams;
 
 /* Device-resident planes of one key frame (for a GPU consumer such as a device-side CARV feed).
@@ -99,6 +105,34 @@ int sd_interkf_check(sd_ctx* ctx, int kf_id, const int* nbr_ids, int n);
 
 /* UpdateSemiDensePointSet, PM.cc:337-367 (uses depth_checked when present, else depth). */
 int sd_update_pointset(sd_ctx* ctx, int kf_id);
+/* InterKeyFrameDepthChecking followed by UpdateSemiDensePointSet, as PM.cc:302-304 calls them, in one kernel launch:
+ * same results as sd_interkf_check + sd_update_pointset. */
+int sd_interkf_check_points(sd_ctx* ctx, int kf_id, const int* nbr_ids, int n);
+
+/* The loop of ProbabilityMapping::SemiDenseLoop over many key frames (PM.cc:137-257 per key frame, then PM.cc:262-307)
+ * issued by one call: sd_semidense for every item in order, and -- with SD_LOOP_INTERKF -- sd_interkf_check_points of an
+ * item as soon as the maps of all its neighbours have been queued (neighbours outside the list must already have maps;
+ * an item whose neighbours lack them is skipped like PM.cc:289-297 and reported in inter_done).  Downloads (dense or
+ * compact, see below) of an item's results are queued right after its last stage when the item asks for them. */
+enum { SD_LOOP_INTERKF = 1 };
+enum { SD_DL_NONE = 0, SD_DL_DENSE = 1, SD_DL_DENSE_POINTS = 2, SD_DL_COMPACT = 3, SD_DL_COMPACT_POINTS = 4 };
+typedef struct SdLoopItem {
+    int kf_id;
+    const int* nbr_ids;       /* n covisible key frames, best first (PM.cc:151-160) */
+    const float* nbr_rot_deg; /* median in-plane rotation per neighbour (PM.cc:170-179); NULL = zeros */
+    int n;
+    float min_invdepth, max_invdepth; /* StereoSearchConstraints (PM.cc:184) */
+    int finish_only;          /* 1: the key frame already has its maps (an earlier call queued sd_semidense): only the
+                               * inter-key-frame stage and the download are issued for it */
+    int download;             /* SD_DL_*: host buffers below, pinned, valid until the next sd_sync */
+    float* out_depth;         /* SD_DL_DENSE*: W*H floats each */
+    float* out_sigma;
+    float* out_points;        /* SD_DL_DENSE_POINTS: H*3W floats */
+    void* out_records;        /* SD_DL_COMPACT*: `capacity` SdCompactDepth / SdCompactPoint records */
+    int capacity;
+    int* out_count;           /* SD_DL_COMPACT*: records available (copy stops at capacity); written by sd_sync at the latest */
+} SdLoopItem;
+int sd_semidense_loop(sd_ctx* ctx, const SdLoopItem* items, int n_items, int flags, int* inter_done /* nullable, n_items */);
 
 /* Confident semi-dense points of one key frame, compacted on the device: the feed for the CARV transcript
  * (extra 3-D points per key frame enter the Delaunay carving through
@@ -116,12 +150,26 @@ int sd_confident_points(sd_ctx* ctx, int kf_id, double max_sigma, int max_points
  * *confident (nullable) = pixels passing the predicate before the max_points cut. */
 int sd_confident_points_device(sd_ctx* ctx, int kf_id, double max_sigma, int max_points, const float** xyz_dev,
                                const float** sigma_dev, const uint32_t** pixel_dev, int* count, int* confident);
+/* Copy (up to capacity entries of) the result the last sd_confident_points_device call left on the device. */
+int sd_confident_points_fetch(sd_ctx* ctx, int capacity, float* xyz, float* sigma, uint32_t* pixel, int* count);
 
 /* Copy results to host buffers (each may be NULL): depth = depth_checked when the inter-KF stage
  * ran, else the intra-KF map; W*H floats each, points H*3W floats.  Synchronises. */
 int sd_download(sd_ctx* ctx, int kf_id, float* depth, float* sigma, float* points);
 /* Asynchronous variant for pinned host buffers; completes at the next sd_sync. */
 int sd_download_async(sd_ctx* ctx, int kf_id, float* depth, float* sigma, float* points);
+/* Compact form of the same results: one record per pixel that carries a depth or a sigma (about a quarter of the
+ * pixels), in no particular order; every other pixel of depth_map_ / depth_sigma_ / SemiDensePointSets_ is zero.
+ * `depth` is depth_checked when the inter-key-frame stage ran, else the intra-key-frame map; x, y, z is the pixel's
+ * entry of SemiDensePointSets_ (needs sd_update_pointset / sd_interkf_check_points).  The host expands the records into
+ * the dense planes (ProbabilityMapping::FetchResults does); a 720p key frame moves ~3 MB (~6 MB with points) instead of
+ * 7.4 MB (18.4 MB).  The async variant completes at the next sd_sync: the record count is only known on the device, so
+ * the copy itself is issued by a later sd_* call on this context once the count has arrived.  *count = records available
+ * (the copy stops at capacity).  Key frames whose maps came from sd_import_maps cannot be downloaded this way. */
+typedef struct SdCompactDepth { uint32_t pixel /* y << 16 | x */; float depth, sigma; } SdCompactDepth;
+typedef struct SdCompactPoint { uint32_t pixel; float depth, sigma, x, y, z; } SdCompactPoint;
+int sd_download_compact(sd_ctx* ctx, int kf_id, int with_points, int capacity, void* records, int* count);
+int sd_download_compact_async(sd_ctx* ctx, int kf_id, int with_points, int capacity, void* records, int* count);
 /* Any single plane, for tests: 0 grad, 1 theta, 2 depth (intra), 3 sigma, 4 depth_checked, 5 points. */
 int sd_download_plane(sd_ctx* ctx, int kf_id, int which, float* out);
 int sd_get_istddev(sd_ctx* ctx, int kf_id, float* out);        /* KeyFrame::I_stddev */
@@ -132,6 +180,27 @@ int sd_device_ptrs(sd_ctx* ctx, int kf_id, SdDevicePlanes* out);
 int sd_import_maps(sd_ctx* ctx, int kf_id, const float* depth_dev, const float* sigma_dev);
 /* Pack the (depth, sigma) maps of a key frame into device buffers (tightly packed W*H floats). */
 int sd_export_maps(sd_ctx* ctx, int kf_id, float* depth_dev, float* sigma_dev);
+/* Same as sd_import_maps from HOST buffers (W*H floats each): how the host class re-installs the maps of a key frame
+ * whose device planes it had released (sd_release_keyframe) when its pose changes later (PM.cc:321-334). */
+int sd_import_maps_host(sd_ctx* ctx, int kf_id, const float* depth, const float* sigma);
+
+/* ---- multi-GPU: the one exchange step of the path ----
+ * Key frames are sharded by index range, one context (one process) per GPU; InterKeyFrameDepthChecking (PM.cc:705-752)
+ * reads the (depth, sigma) maps of neighbours owned by other ranks.  sd_halo_exchange sends the maps of this rank's
+ * boundary key frames and receives the halo key frames' maps with grouped ncclSend / ncclRecv straight out of / into the
+ * key-frame planes on the context's compute stream (no staging copies).  NCCL is loaded with dlopen("libnccl.so.2") at
+ * sd_comm_init time; libsdpm.so itself does not link it. */
+int sd_nccl_unique_id(void* id128 /* 128 bytes out; rank 0 calls this and distributes the bytes */);
+int sd_comm_init(sd_ctx* ctx, int world, int rank, const void* id128);
+int sd_comm_destroy(sd_ctx* ctx);
+typedef struct SdHaloPeer {
+    int peer;            /* rank */
+    int n_send;
+    const int* send_ids; /* key frames of ours the peer needs, ascending; their maps must exist (sd_semidense) */
+    int n_recv;
+    const int* recv_ids; /* key frames of the peer we need, ascending; must be resident here (sd_upload_keyframe) */
+} SdHaloPeer;
+int sd_halo_exchange(sd_ctx* ctx, const SdHaloPeer* peers, int n_peers);
 
 int sd_sync(sd_ctx* ctx);
 const char* sd_last_error(sd_ctx* ctx);

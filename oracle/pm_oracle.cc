@@ -551,8 +551,10 @@ static void SemiDenseLoop(Oracle& O, KeyFrame& kf, const std::vector<const KeyFr
     kf.semidense_flag_ = true;
 }
 
-// PM.cc:628-799 InterKeyFrameDepthChecking, snapshot semantics (H1): reads depth_map_ of the
-// current KF and of the neighbours, writes depth_checked_.
+// PM.cc:628-799 InterKeyFrameDepthChecking.  Default: snapshot semantics (H1): reads depth_map_ of the
+// current KF and of the neighbours, writes depth_checked_.  With P.interkf_inplace the neighbours that
+// were checked by an earlier call are read as checked, which is what the reference's in-place writes
+// amount to for a given visiting order (the caller's call order; the reference's is Map pointer order).
 static void InterKeyFrameDepthChecking(Oracle& O, KeyFrame& cur, const std::vector<const KeyFrame*>& neighbors) {
     const OraParams& P = O.P;
     std::vector<M33> Rji;
@@ -610,8 +612,12 @@ static void InterKeyFrameDepthChecking(Oracle& O, KeyFrame& cur, const std::vect
                 int y1 = y0 + 1;
                 const int ty[4] = {y0, y1, y0, y1};
                 const int tx[4] = {x0, x0, x1, x1};
+                // snapshot (H1): the neighbour's intra-key-frame map.  In-place mode (PM.cc:764, 793 write depth_map_ inside the
+                // loop over key frames, PM.cc:262-307): a neighbour that was checked before reads as checked.
+                const std::vector<float>& ndm =
+                    (P.interkf_inplace && pKFj->interKF_depth_flag_ && pKFj != &cur) ? pKFj->depth_checked_ : pKFj->depth_map_;
                 for (int t = 0; t < 4; ++t) {  // PM.cc:705-752, four unrolled copies
-                    float d = at(pKFj->depth_map_, *pKFj, ty[t], tx[t]);
+                    float d = at(ndm, *pKFj, ty[t], tx[t]);
                     float sigma = at(pKFj->depth_sigma_, *pKFj, ty[t], tx[t]);
                     if (d > 0.000001) {
                         float test = std::pow((double)(depthj - d), 2) / std::pow((double)sigma, 2);
@@ -719,6 +725,7 @@ void ora_default_params(OraParams* p) {
     p->chi2_inter = 3.84;
     p->slope_limit = 4;
     p->border = 2;
+    p->interkf_inplace = 0;
 }
 
 void* ora_create(const OraParams* p) {

@@ -30,6 +30,7 @@ typedef struct OraParams {
     double chi2_inter;  /* PM.cc:710      = 3.84                                           */
     float slope_limit;  /* PM.cc:393 = 4                                                  */
     int   border;       /* PM.cc:198-199 = 2                                              */
+    int   interkf_inplace; /* 0: snapshot inter-KF check (H1); 1: PM.cc:764,793 in place, in call order */
 } OraParams;
 
 void ora_default_params(OraParams* p);

@@ -26,6 +26,7 @@ class OraParams(C.Structure):
         ("chi2_inter", C.c_double),
         ("slope_limit", C.c_float),
         ("border", C.c_int),
+        ("interkf_inplace", C.c_int),
     ]
 
 

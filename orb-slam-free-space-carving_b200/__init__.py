@@ -32,7 +32,26 @@ class SdError(RuntimeError):
 class SdParams(C.Structure):
     _fields_ = [("lambdaG", C.c_float), ("lambdaL", C.c_float), ("lambdaTheta", C.c_float), ("lambdaN", C.c_int),
                 ("theta", C.c_double), ("chi2_fuse", C.c_double), ("chi2_inter", C.c_double),
-                ("slope_limit", C.c_float), ("border", C.c_int)]
+                ("slope_limit", C.c_float), ("border", C.c_int), ("interkf_inplace", C.c_int)]
+
+
+class SdLoopItem(C.Structure):
+    _fields_ = [("kf_id", C.c_int), ("nbr_ids", C.POINTER(C.c_int)), ("nbr_rot_deg", C.POINTER(C.c_float)), ("n", C.c_int),
+                ("min_invdepth", C.c_float), ("max_invdepth", C.c_float), ("finish_only", C.c_int), ("download", C.c_int),
+                ("out_depth", C.c_void_p), ("out_sigma", C.c_void_p), ("out_points", C.c_void_p),
+                ("out_records", C.c_void_p), ("capacity", C.c_int), ("out_count", C.POINTER(C.c_int))]
+
+
+class SdHaloPeer(C.Structure):
+    _fields_ = [("peer", C.c_int), ("n_send", C.c_int), ("send_ids", C.POINTER(C.c_int)), ("n_recv", C.c_int),
+                ("recv_ids", C.POINTER(C.c_int))]
+
+
+SD_LOOP_INTERKF = 1
+SD_DL_NONE, SD_DL_DENSE, SD_DL_DENSE_POINTS, SD_DL_COMPACT, SD_DL_COMPACT_POINTS = range(5)
+# records of sd_download_compact (include/sdpm.h: SdCompactDepth / SdCompactPoint)
+COMPACT_DEPTH = np.dtype([("pixel", "<u4"), ("depth", "<f4"), ("sigma", "<f4")])
+COMPACT_POINT = np.dtype([("pixel", "<u4"), ("depth", "<f4"), ("sigma", "<f4"), ("x", "<f4"), ("y", "<f4"), ("z", "<f4")])
 
 
 class SdDevicePlanes(C.Structure):
@@ -56,6 +75,16 @@ SYMBOLS = {
     "sd_semidense": (C.c_int, [_vp, C.c_int, _ip, _fp, C.c_int, C.c_float, C.c_float]),
     "sd_interkf_check": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
     "sd_update_pointset": (C.c_int, [_vp, C.c_int]),
+    "sd_interkf_check_points": (C.c_int, [_vp, C.c_int, _ip, C.c_int]),
+    "sd_semidense_loop": (C.c_int, [_vp, C.POINTER(SdLoopItem), C.c_int, C.c_int, _ip]),
+    "sd_download_compact": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _ip]),
+    "sd_download_compact_async": (C.c_int, [_vp, C.c_int, C.c_int, C.c_int, _vp, _ip]),
+    "sd_confident_points_fetch": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp, _ip]),
+    "sd_import_maps_host": (C.c_int, [_vp, C.c_int, _vp, _vp]),
+    "sd_nccl_unique_id": (C.c_int, [_vp]),
+    "sd_comm_init": (C.c_int, [_vp, C.c_int, C.c_int, _vp]),
+    "sd_comm_destroy": (C.c_int, [_vp]),
+    "sd_halo_exchange": (C.c_int, [_vp, C.POINTER(SdHaloPeer), C.c_int]),
     "sd_confident_points": (C.c_int, [_vp, C.c_int, C.c_double, C.c_int, C.c_int, _vp, _vp, _vp, _ip]),
     "sd_confident_points_device": (C.c_int, [_vp, C.c_int, C.c_double, C.c_int, C.POINTER(_vp), C.POINTER(_vp), C.POINTER(_vp), _ip, _ip]),
     "sd_download": (C.c_int, [_vp, C.c_int, _vp, _vp, _vp]),
@@ -116,6 +145,29 @@ def default_params():
     p = SdParams()
     lib().sd_default_params(C.byref(p))
     return p
+
+
+def nccl_unique_id():
+    """128 bytes from ncclGetUniqueId (rank 0 calls this and distributes them)."""
+    buf = C.create_string_buffer(128)
+    rc = lib().sd_nccl_unique_id(buf)
+    if rc:
+        raise SdError(rc, "sd_nccl_unique_id (libnccl.so.2 not loadable?)")
+    return buf.raw
+
+
+def expand_compact(records, h, w, points=False):
+    """Dense (depth, sigma[, points]) planes from compact records: what ProbabilityMapping::FetchResults does in C++."""
+    d = np.zeros((h, w), np.float32)
+    s = np.zeros((h, w), np.float32)
+    y, x = (records["pixel"] >> 16).astype(np.int64), (records["pixel"] & 0xffff).astype(np.int64)
+    d[y, x] = records["depth"]
+    s[y, x] = records["sigma"]
+    if not points:
+        return d, s
+    p = np.zeros((h, 3 * w), np.float32)
+    p[y, 3 * x], p[y, 3 * x + 1], p[y, 3 * x + 2] = records["x"], records["y"], records["z"]
+    return d, s, p
 
 
 def stereo_search_constraints(depths):
@@ -214,6 +266,84 @@ class Context:
 
     def update_pointset(self, kf_id):
         self._ck(self.L.sd_update_pointset(self.h, int(kf_id)))
+
+    def interkf_check_points(self, kf_id, nbr_ids):
+        """InterKeyFrameDepthChecking + UpdateSemiDensePointSet (PM.cc:302-304) in one launch."""
+        ids, ip = _i(nbr_ids)
+        self._ck(self.L.sd_interkf_check_points(self.h, int(kf_id), ip, len(ids)))
+
+    def make_loop(self, items, interkf=True):
+        """Marshal a key-frame list for sd_semidense_loop once (the arrays stay alive with the returned object).
+        items: dicts with kf_id, nbrs, rots, prior=(min, max) and optional download=(mode, ...) entries:
+        (SD_DL_DENSE, depth_ptr, sigma_ptr), (SD_DL_DENSE_POINTS, depth_ptr, sigma_ptr, points_ptr),
+        (SD_DL_COMPACT | SD_DL_COMPACT_POINTS, records_ptr, capacity, count_ptr)."""
+        arr = (SdLoopItem * len(items))()
+        keep = []
+        for a, it in zip(arr, items):
+            ids, ip = _i(it["nbrs"])
+            rot, rp = _f(it["rots"])
+            keep += [ids, rot]
+            a.kf_id, a.nbr_ids, a.nbr_rot_deg, a.n = int(it["kf_id"]), ip, rp, len(ids)
+            a.min_invdepth, a.max_invdepth = float(it["prior"][0]), float(it["prior"][1])
+            a.finish_only = 1 if it.get("finish_only") else 0
+            dl = it.get("download")
+            a.download = SD_DL_NONE
+            if dl:
+                a.download = int(dl[0])
+                if dl[0] in (SD_DL_DENSE, SD_DL_DENSE_POINTS):
+                    a.out_depth, a.out_sigma = dl[1], dl[2]
+                    a.out_points = dl[3] if dl[0] == SD_DL_DENSE_POINTS else None
+                else:
+                    a.out_records, a.capacity = dl[1], int(dl[2])
+                    a.out_count = C.cast(dl[3], C.POINTER(C.c_int)) if dl[3] else None
+        done = np.zeros(len(items), np.int32)
+        return {"arr": arr, "n": len(items), "flags": SD_LOOP_INTERKF if interkf else 0, "keep": keep, "done": done}
+
+    def semidense_loop(self, loop):
+        """SemiDenseLoop over a key-frame list in one C call (PM.cc:137-307); returns the per-item inter-KF flags."""
+        self._ck(self.L.sd_semidense_loop(self.h, loop["arr"], loop["n"], loop["flags"], loop["done"].ctypes.data_as(_ip)))
+        return loop["done"]
+
+    def download_compact(self, kf_id, points=False, capacity=None):
+        """Records (numpy structured array, COMPACT_DEPTH / COMPACT_POINT) of the pixels that carry a depth or a sigma."""
+        h, w = self.shape
+        cap = int(capacity) if capacity is not None else (w - 4) * (h - 4)
+        rec = np.empty(cap, COMPACT_POINT if points else COMPACT_DEPTH)
+        n = C.c_int()
+        self._ck(self.L.sd_download_compact(self.h, int(kf_id), 1 if points else 0, cap, rec.ctypes.data, C.byref(n)))
+        return rec[:min(n.value, cap)], n.value
+
+    def download_compact_async_ptr(self, kf_id, points, capacity, records_ptr, count_ptr):
+        self._ck(self.L.sd_download_compact_async(self.h, int(kf_id), 1 if points else 0, int(capacity), records_ptr,
+                                                  C.cast(count_ptr, _ip) if count_ptr else None))
+
+    def import_maps_host(self, kf_id, depth, sigma):
+        d = np.ascontiguousarray(depth, np.float32)
+        s = np.ascontiguousarray(sigma, np.float32)
+        self._ck(self.L.sd_import_maps_host(self.h, int(kf_id), d.ctypes.data, s.ctypes.data))
+
+    # ---- multi-GPU: NCCL halo exchange behind the C ABI ----
+    def comm_init(self, world, rank, unique_id: bytes):
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._ck(self.L.sd_comm_init(self.h, int(world), int(rank), buf))
+
+    def comm_destroy(self):
+        self._ck(self.L.sd_comm_destroy(self.h))
+
+    def make_halo(self, send, recv):
+        """send / recv: {peer: [key-frame ids]} -> marshalled SdHaloPeer array (kept alive by the returned object)."""
+        peers = sorted(set(send) | set(recv))
+        arr = (SdHaloPeer * max(len(peers), 1))()
+        keep = []
+        for a, p in zip(arr, peers):
+            si, sp = _i(sorted(send.get(p, [])))
+            ri, rp = _i(sorted(recv.get(p, [])))
+            keep += [si, ri]
+            a.peer, a.n_send, a.send_ids, a.n_recv, a.recv_ids = int(p), len(si), sp, len(ri), rp
+        return {"arr": arr, "n": len(peers), "keep": keep}
+
+    def halo_exchange(self, halo):
+        self._ck(self.L.sd_halo_exchange(self.h, halo["arr"], halo["n"]))
 
     def confident_points(self, kf_id, max_sigma=0.01, max_points=0, capacity=None):
         """(xyz [n,3], sigma [n], pixel [n] = y << 16 | x, count) of the pixels PM.cc:120-121 keeps; see sd_confident_points."""

@@ -2,6 +2,7 @@
 // device-resident key-frame planes, the three streams (upload+K0 / K1..K5 / download) and the
 // per-pair host math.  No CPU fallback exists: every stage is a kernel launch.
 #include <cuda_runtime.h>
+#include <dlfcn.h>
 
 #include <algorithm>
 #include <cmath>
@@ -37,6 +38,7 @@ struct Slot {
     uint32_t* vlist = nullptr;  // pixels carrying a depth after the intra-KF stage (k23_intra), input of k4_inter_check
     KfMeta* meta = nullptr;
     bool vlist_ok = false;      // vlist / meta->valid_count describe `depth`
+    bool vlist_from_import = false;  // the list was rebuilt from imported planes (which may carry values outside the 2-px frame)
     bool has_semidense = false, has_checked = false, has_points = false, pose_changed = false;
     cudaEvent_t ev_up = nullptr;  // upload + K0 done (s_up)
     cudaEvent_t ev_dn = nullptr;  // last download issued (s_dn)
@@ -93,6 +95,28 @@ struct sd_ctx {
     uint8_t* conf_out = nullptr;  // cap x (xyz, sigma, pixel)
     int conf_cap = 0;
     int* h_conf = nullptr;        // pinned: {total, confident}
+    const float* conf_last_xyz = nullptr;   // result of the last sd_confident_points_device call (device)
+    const float* conf_last_sigma = nullptr;
+    const uint32_t* conf_last_pix = nullptr;
+    int conf_last_count = 0;
+    // compact downloads (k7_pack): ring of device staging buffers; the record count of a key frame is only known on the
+    // device, so the device->host copy of a pending download is issued once its count has arrived (poll_pack)
+    static const int PACK_RING = 16;
+    struct PackSlot {
+        uint8_t* dev = nullptr;     // [int count | pad to 256 B | cap records]
+        int* h_count = nullptr;     // pinned
+        cudaEvent_t ev_cnt = nullptr;
+        void* host_records = nullptr;
+        int capacity = 0, stride = 0;
+        int* count_out = nullptr;
+    };
+    PackSlot pack[PACK_RING];
+    long long pack_head = 0, pack_tail = 0;  // pending downloads: [head, tail)
+    int pack_cap = 0;
+    // NCCL (dlopen), one communicator per context
+    void* nccl_lib = nullptr;
+    void* nccl_comm = nullptr;
+    int nccl_world = 0, nccl_rank = -1;
 };
 
 namespace {
@@ -267,7 +291,7 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         CU(c, cudaEventRecord(c->ev_tmp, c->s_dn));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
     }
-    s->has_semidense = s->has_checked = s->has_points = s->pose_changed = s->vlist_ok = false;
+    s->has_semidense = s->has_checked = s->has_points = s->pose_changed = s->vlist_ok = s->vlist_from_import = false;
     s->dn_pending = false;
     s->sd_recorded = s->chk_recorded = false;
     s->rd_idx = -1;
@@ -282,8 +306,6 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         k0_gradient<<<grd, blk, 0, c->s_up>>>(s->gray, c->pitch_u8, w, h, s->grad, s->theta, c->pitch_f, s->arc, c->arc_pitch,
                                               s->list, s->meta, c->P.lambdaG, c->P.lambdaTheta, c->P.border);
     }
-    k0_finalize<<<1, 1, 0, c->s_up>>>(s->meta, w, h);
-    c->launches++;
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_up, c->s_up));
     return SD_OK;
@@ -297,6 +319,37 @@ cudaError_t wait_map_readers(sd_ctx* c, Slot* s, cudaStream_t stream) {
     if (s->rd_idx >= 0) e = cudaStreamWaitEvent(stream, c->ev_ring[s->rd_idx % sd_ctx::RING], 0);
     if (e == cudaSuccess && s->chk_recorded) e = cudaStreamWaitEvent(stream, s->ev_chk, 0);
     return e;
+}
+
+
+// ---- compact downloads: pending queue ----
+// issue the device->host copy of pending download `i` (its count has arrived in pinned memory)
+cudaError_t pack_issue(sd_ctx* c, long long i) {
+    sd_ctx::PackSlot& ps = c->pack[i % sd_ctx::PACK_RING];
+    const int avail = *ps.h_count;
+    if (ps.count_out) *ps.count_out = avail;
+    const int ncopy = std::min(avail, ps.capacity);
+    cudaError_t e = cudaSuccess;
+    if (ncopy > 0 && ps.host_records)
+        e = cudaMemcpyAsync(ps.host_records, ps.dev + 256, (size_t)ncopy * ps.stride, cudaMemcpyDeviceToHost, c->s_dn);
+    ps.host_records = nullptr;
+    ps.count_out = nullptr;
+    return e;
+}
+
+// drain == false: issue the copies of the pending downloads whose count has arrived (no waiting);
+// drain == true: wait for every count and issue every copy
+cudaError_t poll_pack(sd_ctx* c, bool drain) {
+    while (c->pack_head < c->pack_tail) {
+        sd_ctx::PackSlot& ps = c->pack[c->pack_head % sd_ctx::PACK_RING];
+        cudaError_t q = drain ? cudaEventSynchronize(ps.ev_cnt) : cudaEventQuery(ps.ev_cnt);
+        if (q == cudaErrorNotReady) return cudaSuccess;
+        if (q != cudaSuccess) return q;
+        cudaError_t e = pack_issue(c, c->pack_head);
+        if (e != cudaSuccess) return e;
+        c->pack_head++;
+    }
+    return cudaSuccess;
 }
 
 void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
@@ -340,6 +393,7 @@ int sd_default_params(SdParams* p) {
     p->chi2_inter = 3.84;
     p->slope_limit = 4;
     p->border = 2;
+    p->interkf_inplace = 0;
     return SD_OK;
 }
 
@@ -352,7 +406,9 @@ int sd_create(int device, const SdParams* params, sd_ctx** out) {
     sd_ctx* c = new sd_ctx();
     c->device = device;
     if (params) c->P = *params; else sd_default_params(&c->P);
-    if (c->P.border < 1 || c->P.lambdaN < 1 || !(c->P.theta > 0) || !(c->P.lambdaTheta >= 0) || !(c->P.lambdaL >= 0)) {
+    // border: the reference hard-codes the 2-pixel frame in every loop (PM.cc:198-199, 492, 555, 659, 342); the field
+    // exists so that the struct mirrors the literal, but no other value has a reference behaviour to match
+    if (c->P.border != 2 || c->P.lambdaN < 1 || !(c->P.theta > 0) || !(c->P.lambdaTheta >= 0) || !(c->P.lambdaL >= 0)) {
         delete c;
         return SD_ERR_INVALID_ARG;
     }
@@ -427,6 +483,12 @@ int sd_destroy(sd_ctx* c) {
     cudaFree(c->conf_seg);
     cudaFree(c->conf_out);
     if (c->h_conf) cudaFreeHost(c->h_conf);
+    for (auto& ps : c->pack) {
+        cudaFree(ps.dev);
+        if (ps.h_count) cudaFreeHost(ps.h_count);
+        if (ps.ev_cnt) cudaEventDestroy(ps.ev_cnt);
+    }
+    sd_comm_destroy(c);
     cudaStreamDestroy(c->s_up);
     cudaStreamDestroy(c->s_main);
     cudaStreamDestroy(c->s_srch);
@@ -472,6 +534,7 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     Slot* s = find(c, kf_id);
     if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
     CU(c, cudaSetDevice(c->device));
+    CU(c, poll_pack(c, false));
     static thread_local SearchArgs A;
     fill_search_common(c, s, A);
     A.n = n;
@@ -556,17 +619,19 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     s->sd_recorded = true;
     s->has_semidense = true;
     s->vlist_ok = true;
+    s->vlist_from_import = false;
     s->has_checked = false;
     s->has_points = false;
     return SD_OK;
 }
 
-int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
+static int interkf_common(sd_ctx* c, int kf_id, const int* nbr_ids, int n, bool with_points) {
     if (!c || !nbr_ids || n < 1 || n > SD_MAX_NEIGHBOURS) return fail(c, SD_ERR_INVALID_ARG, "sd_interkf_check: bad argument (n=%d)", n);
     Slot* s = find(c, kf_id);
     if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     CU(c, cudaSetDevice(c->device));
+    CU(c, poll_pack(c, false));
     static thread_local InterArgs A;
     A.W = c->W; A.H = c->H; A.pitch_f = c->pitch_f; A.n = n; A.lambdaN = c->P.lambdaN;
     A.fx = s->K[0]; A.fy = s->K[1]; A.cx = s->K[2]; A.cy = s->K[3];
@@ -575,6 +640,7 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
     A.depth_out = s->depth_chk;
     A.vlist = s->vlist;
     A.vcount = &s->meta->valid_count;
+    const bool inplace = c->P.interkf_inplace != 0;
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
         if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
@@ -583,7 +649,9 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
         geom::relative_pose(s->Rcw, s->tcw, nb->Rcw, nb->tcw, N.R, N.t);
         for (int k = 0; k < 3; ++k) { N.Rd2[k] = (double)N.R[6 + k]; N.td[k] = (double)N.t[k]; }
         N.fx = nb->K[0]; N.fy = nb->K[1]; N.cx = nb->K[2]; N.cy = nb->K[3];
-        N.depth = nb->depth;
+        // in-place mode (PM.cc:764, 793): a neighbour that has been checked already is read as checked; its K4 ran
+        // earlier on this same stream, so the read is ordered after it
+        N.depth = (inplace && nb->has_checked && nb != s) ? nb->depth_chk : nb->depth;
         N.sigma = nb->sigma;
         if (nb->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, nb->ev_sd, 0));
     }
@@ -597,17 +665,28 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
         CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_chk));
         CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_chk));
         dim3 grd((c->W + 31) / 32, (c->H + 7) / 8);
-        k_build_vlist<<<grd, 256, 0, c->s_chk>>>(s->depth, c->pitch_f, c->W, c->H, s->vlist, &s->meta->valid_count);
+        k_build_vlist<<<grd, 256, 0, c->s_chk>>>(s->depth, s->sigma, c->pitch_f, c->W, c->H, s->vlist, &s->meta->valid_count);
         c->launches++;
         s->vlist_ok = true;
+        s->vlist_from_import = true;
     } else if (s->has_checked) {  // a repeated check starts again from the intra-KF map
         const size_t pb = (size_t)c->pitch_f * sizeof(float);
         CU(c, cudaMemcpy2DAsync(s->depth_chk, pb, s->depth, pb, (size_t)c->W * sizeof(float), c->H, cudaMemcpyDeviceToDevice, c->s_chk));
     }
+    if (with_points) {
+        if (!s->points) CU(c, cudaMalloc(&s->points, (size_t)c->W * c->H * 3 * sizeof(float)));
+        A.P.W = c->W; A.P.H = c->H; A.P.pitch_f = c->pitch_f;
+        A.P.fx = s->K[0]; A.P.fy = s->K[1]; A.P.cx = s->K[2]; A.P.cy = s->K[3];
+        std::memcpy(A.P.Twc, s->Twc, sizeof(A.P.Twc));
+        A.P.depth = s->depth_chk;
+        A.P.points = s->points;
+        CU(c, cudaMemsetAsync(s->points, 0, (size_t)c->W * c->H * 3 * sizeof(float), c->s_chk));
+    }
     {
         ScopedTimer t(c, c->s_chk, T_INTER);
         const int worst = (c->W - 4) * (c->H - 4);  // the list holds pixels inside the 2-px frame only
-        k4_inter_check<<<(worst + 127) / 128, 128, 0, c->s_chk>>>(A);
+        if (with_points) k4_inter_check<true><<<(worst + 127) / 128, 128, 0, c->s_chk>>>(A);
+        else k4_inter_check<false><<<(worst + 127) / 128, 128, 0, c->s_chk>>>(A);
     }
     CU(c, cudaGetLastError());
     {   // this launch read the maps of kf and of its neighbours: writers of those maps wait for it
@@ -619,9 +698,14 @@ int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) {
         s->chk_recorded = true;
     }
     s->has_checked = true;
-    s->has_points = false;
+    s->has_points = with_points;
+    if (with_points) s->pose_changed = false;
     return SD_OK;
 }
+
+int sd_interkf_check(sd_ctx* c, int kf_id, const int* nbr_ids, int n) { return interkf_common(c, kf_id, nbr_ids, n, false); }
+
+int sd_interkf_check_points(sd_ctx* c, int kf_id, const int* nbr_ids, int n) { return interkf_common(c, kf_id, nbr_ids, n, true); }
 
 int sd_update_pointset(sd_ctx* c, int kf_id) {
     if (!c) return SD_ERR_INVALID_ARG;
@@ -675,6 +759,7 @@ int sd_confident_points_device(sd_ctx* c, int kf_id, double max_sigma, int max_p
         cudaFree(c->conf_out);
         c->conf_out = nullptr;
         c->conf_cap = 0;
+        c->conf_last_xyz = nullptr;
         CU(c, cudaMalloc(&c->conf_out, (size_t)cap * 5 * sizeof(float)));
         c->conf_cap = cap;
     }
@@ -719,6 +804,7 @@ int sd_confident_points_device(sd_ctx* c, int kf_id, double max_sigma, int max_p
     s->chk_recorded = true;
     CU(c, cudaStreamSynchronize(st));
     *count = c->h_conf[0];
+    c->conf_last_xyz = A.out_xyz; c->conf_last_sigma = A.out_sigma; c->conf_last_pix = A.out_pix; c->conf_last_count = c->h_conf[0];
     if (confident) *confident = c->h_conf[1];
     if (xyz_dev) *xyz_dev = A.out_xyz;
     if (sigma_dev) *sigma_dev = A.out_sigma;
@@ -733,11 +819,20 @@ int sd_confident_points(sd_ctx* c, int kf_id, double max_sigma, int max_points, 
     const uint32_t* dp = nullptr;
     int rc = sd_confident_points_device(c, kf_id, max_sigma, max_points, &dx, &ds, &dp, count, nullptr);
     if (rc != SD_OK) return rc;
-    const size_t n = (size_t)std::min(*count, capacity);
+    int n = 0;
+    return sd_confident_points_fetch(c, capacity, xyz, sigma, pixel, &n);
+}
+
+int sd_confident_points_fetch(sd_ctx* c, int capacity, float* xyz, float* sigma, uint32_t* pixel, int* count) {
+    if (!c || !count || capacity < 0) return SD_ERR_INVALID_ARG;
+    if (!c->conf_last_xyz) return fail(c, SD_ERR_NOT_READY, "sd_confident_points_fetch: no device-resident result");
+    CU(c, cudaSetDevice(c->device));
+    *count = c->conf_last_count;
+    const size_t n = (size_t)std::min(c->conf_last_count, capacity);
     if (n) {
-        if (xyz) CU(c, cudaMemcpyAsync(xyz, dx, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->s_chk));
-        if (sigma) CU(c, cudaMemcpyAsync(sigma, ds, n * sizeof(float), cudaMemcpyDeviceToHost, c->s_chk));
-        if (pixel) CU(c, cudaMemcpyAsync(pixel, dp, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->s_chk));
+        if (xyz) CU(c, cudaMemcpyAsync(xyz, c->conf_last_xyz, n * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->s_chk));
+        if (sigma) CU(c, cudaMemcpyAsync(sigma, c->conf_last_sigma, n * sizeof(float), cudaMemcpyDeviceToHost, c->s_chk));
+        if (pixel) CU(c, cudaMemcpyAsync(pixel, c->conf_last_pix, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->s_chk));
         CU(c, cudaStreamSynchronize(c->s_chk));
     }
     return SD_OK;
@@ -764,6 +859,66 @@ int sd_download_async(sd_ctx* c, int kf_id, float* depth, float* sigma, float* p
 int sd_download(sd_ctx* c, int kf_id, float* depth, float* sigma, float* points) {
     int rc = sd_download_async(c, kf_id, depth, sigma, points);
     if (rc != SD_OK) return rc;
+    CU(c, cudaStreamSynchronize(c->s_dn));
+    return SD_OK;
+}
+
+
+int sd_download_compact_async(sd_ctx* c, int kf_id, int with_points, int capacity, void* records, int* count) {
+    if (!c || capacity < 0 || (capacity > 0 && !records)) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
+    if (!s->vlist_ok || s->vlist_from_import)
+        return fail(c, SD_ERR_NOT_READY, "key frame %d: maps were imported, no compact form (use sd_download)", kf_id);
+    if (with_points && !s->has_points) return fail(c, SD_ERR_NOT_READY, "key frame %d has no point set", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    CU(c, poll_pack(c, false));
+    if (c->pack_tail - c->pack_head == sd_ctx::PACK_RING) {  // ring full: the oldest pending download must go out first
+        sd_ctx::PackSlot& old = c->pack[c->pack_head % sd_ctx::PACK_RING];
+        CU(c, cudaEventSynchronize(old.ev_cnt));
+        CU(c, pack_issue(c, c->pack_head));
+        c->pack_head++;
+    }
+    const int cap = (c->W - 4) * (c->H - 4);  // the list holds pixels inside the 2-px frame only
+    sd_ctx::PackSlot& ps = c->pack[c->pack_tail % sd_ctx::PACK_RING];
+    if (!ps.dev) {
+        CU(c, cudaMalloc(&ps.dev, 256 + (size_t)cap * sizeof(SdCompactPoint)));
+        CU(c, cudaHostAlloc(&ps.h_count, sizeof(int), cudaHostAllocDefault));
+        CU(c, cudaEventCreateWithFlags(&ps.ev_cnt, cudaEventDisableTiming));
+    }
+    // stream order on s_dn: the copy of this slot's previous use precedes the kernel below
+    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_sd, 0));
+    if (s->chk_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_chk, 0));
+    PackArgs A;
+    A.W = c->W; A.pitch_f = c->pitch_f;
+    A.vlist = s->vlist; A.vcount = &s->meta->valid_count;
+    A.depth = s->has_checked ? s->depth_chk : s->depth;
+    A.sigma = s->sigma;
+    A.points = with_points ? s->points : nullptr;
+    A.with_points = with_points ? 1 : 0;
+    A.out = ps.dev + 256;
+    A.out_count = reinterpret_cast<int*>(ps.dev);
+    A.cap = cap;
+    k7_pack<<<(cap + 255) / 256, 256, 0, c->s_dn>>>(A);
+    c->launches++;
+    CU(c, cudaGetLastError());
+    CU(c, cudaMemcpyAsync(ps.h_count, ps.dev, sizeof(int), cudaMemcpyDeviceToHost, c->s_dn));
+    CU(c, cudaEventRecord(ps.ev_cnt, c->s_dn));
+    CU(c, cudaEventRecord(s->ev_dn, c->s_dn));  // the planes have been read once the kernel is done
+    s->dn_pending = true;
+    ps.host_records = records;
+    ps.capacity = capacity;
+    ps.stride = with_points ? (int)sizeof(SdCompactPoint) : (int)sizeof(SdCompactDepth);
+    ps.count_out = count;
+    c->pack_tail++;
+    return SD_OK;
+}
+
+int sd_download_compact(sd_ctx* c, int kf_id, int with_points, int capacity, void* records, int* count) {
+    int rc = sd_download_compact_async(c, kf_id, with_points, capacity, records, count);
+    if (rc != SD_OK) return rc;
+    CU(c, poll_pack(c, true));
     CU(c, cudaStreamSynchronize(c->s_dn));
     return SD_OK;
 }
@@ -836,6 +991,9 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
     CU(c, cudaSetDevice(c->device));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    // a re-upload of this key frame (or a recycled slot) forgets the slot's reader bookkeeping and makes only s_up
+    // wait for the work still queued on the other streams: order the overwrite of the maps after that upload
+    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
     CU(c, wait_map_readers(c, s, c->s_main));
     if (s->dn_pending) {
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
@@ -851,6 +1009,258 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     return SD_OK;
 }
 
+int sd_import_maps_host(sd_ctx* c, int kf_id, const float* depth, const float* sigma) {
+    if (!c || !depth || !sigma) return SD_ERR_INVALID_ARG;
+    Slot* s = find(c, kf_id);
+    if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
+    CU(c, cudaSetDevice(c->device));
+    const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
+    CU(c, wait_map_readers(c, s, c->s_main));
+    if (s->dn_pending) {
+        CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+        s->dn_pending = false;
+    }
+    CU(c, cudaMemcpy2DAsync(s->depth, pb, depth, wb, wb, c->H, cudaMemcpyHostToDevice, c->s_main));
+    CU(c, cudaMemcpy2DAsync(s->sigma, pb, sigma, wb, wb, c->H, cudaMemcpyHostToDevice, c->s_main));
+    CU(c, cudaEventRecord(s->ev_sd, c->s_main));
+    CU(c, cudaStreamSynchronize(c->s_main));  // the host buffers are borrowed for the call only
+    s->sd_recorded = true;
+    s->has_semidense = true;
+    s->has_checked = false;
+    s->has_points = false;
+    s->vlist_ok = false;
+    return SD_OK;
+}
+
+// ---- NCCL halo exchange (dlopen; minimal local declarations of the NCCL C API) ----
+namespace {
+struct NcclUniqueId { char internal[128]; };
+typedef int (*nccl_get_unique_id_t)(NcclUniqueId*);
+typedef int (*nccl_comm_init_rank_t)(void**, int, NcclUniqueId, int);
+typedef int (*nccl_comm_destroy_t)(void*);
+typedef int (*nccl_group_t)(void);
+typedef int (*nccl_send_t)(const void*, size_t, int, int, void*, cudaStream_t);
+typedef int (*nccl_recv_t)(void*, size_t, int, int, void*, cudaStream_t);
+typedef const char* (*nccl_err_t)(int);
+const int kNcclFloat32 = 7;  // ncclFloat32 in ncclDataType_t
+
+struct NcclApi {
+    void* lib = nullptr;
+    nccl_get_unique_id_t get_unique_id = nullptr;
+    nccl_comm_init_rank_t comm_init_rank = nullptr;
+    nccl_comm_destroy_t comm_destroy = nullptr;
+    nccl_group_t group_start = nullptr, group_end = nullptr;
+    nccl_send_t send = nullptr;
+    nccl_recv_t recv = nullptr;
+    nccl_err_t err = nullptr;
+};
+
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (!tried) {
+        tried = true;
+        // a process that already loaded NCCL (torch ships its own libnccl.so.2) gets that copy back
+        const char* names[] = {getenv("SDPM_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+        for (const char* nm : names) {
+            if (!nm || !*nm) continue;
+            api.lib = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+            if (api.lib) break;
+        }
+        if (api.lib) {
+            api.get_unique_id = (nccl_get_unique_id_t)dlsym(api.lib, "ncclGetUniqueId");
+            api.comm_init_rank = (nccl_comm_init_rank_t)dlsym(api.lib, "ncclCommInitRank");
+            api.comm_destroy = (nccl_comm_destroy_t)dlsym(api.lib, "ncclCommDestroy");
+            api.group_start = (nccl_group_t)dlsym(api.lib, "ncclGroupStart");
+            api.group_end = (nccl_group_t)dlsym(api.lib, "ncclGroupEnd");
+            api.send = (nccl_send_t)dlsym(api.lib, "ncclSend");
+            api.recv = (nccl_recv_t)dlsym(api.lib, "ncclRecv");
+            api.err = (nccl_err_t)dlsym(api.lib, "ncclGetErrorString");
+            if (!api.get_unique_id || !api.comm_init_rank || !api.comm_destroy || !api.group_start || !api.group_end || !api.send ||
+                !api.recv)
+                api.lib = nullptr;
+        }
+    }
+    return api.lib ? &api : nullptr;
+}
+
+#define NC(c, api, call)                                                                                  \
+    do {                                                                                                  \
+        int r__ = (call);                                                                                 \
+        if (r__ != 0) return fail(c, SD_ERR_CUDA, "%s: NCCL error %d (%s)", #call, r__, (api)->err ? (api)->err(r__) : "?"); \
+    } while (0)
+}  // namespace
+
+int sd_nccl_unique_id(void* id128) {
+    if (!id128) return SD_ERR_INVALID_ARG;
+    NcclApi* api = nccl_api();
+    if (!api) return SD_ERR_NOT_READY;
+    NcclUniqueId id;
+    if (api->get_unique_id(&id) != 0) return SD_ERR_CUDA;
+    std::memcpy(id128, &id, sizeof(id));
+    return SD_OK;
+}
+
+int sd_comm_init(sd_ctx* c, int world, int rank, const void* id128) {
+    if (!c || !id128 || world < 1 || rank < 0 || rank >= world) return fail(c, SD_ERR_INVALID_ARG, "sd_comm_init: bad argument");
+    NcclApi* api = nccl_api();
+    if (!api) return fail(c, SD_ERR_NOT_READY, "sd_comm_init: libnccl.so.2 not found (set SDPM_NCCL_LIB)");
+    if (c->nccl_comm) return fail(c, SD_ERR_INVALID_ARG, "sd_comm_init: the context already has a communicator");
+    CU(c, cudaSetDevice(c->device));
+    NcclUniqueId id;
+    std::memcpy(&id, id128, sizeof(id));
+    void* comm = nullptr;
+    NC(c, api, api->comm_init_rank(&comm, world, id, rank));
+    c->nccl_comm = comm;
+    c->nccl_world = world;
+    c->nccl_rank = rank;
+    return SD_OK;
+}
+
+int sd_comm_destroy(sd_ctx* c) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    if (c->nccl_comm) {
+        NcclApi* api = nccl_api();
+        cudaSetDevice(c->device);
+        cudaStreamSynchronize(c->s_main);
+        if (api) api->comm_destroy(c->nccl_comm);
+        c->nccl_comm = nullptr;
+    }
+    return SD_OK;
+}
+
+int sd_halo_exchange(sd_ctx* c, const SdHaloPeer* peers, int n_peers) {
+    if (!c || n_peers < 0 || (n_peers > 0 && !peers)) return fail(c, SD_ERR_INVALID_ARG, "sd_halo_exchange: bad argument");
+    if (n_peers == 0) return SD_OK;
+    if (!c->nccl_comm) return fail(c, SD_ERR_NOT_READY, "sd_halo_exchange: no communicator (sd_comm_init)");
+    NcclApi* api = nccl_api();
+    CU(c, cudaSetDevice(c->device));
+    const size_t plane = (size_t)c->pitch_f * c->H;  // whole pitched planes: every rank of a run has the same geometry
+    // order the receives after everything that may still read (or is still producing) the planes they overwrite
+    for (int p = 0; p < n_peers; ++p) {
+        const SdHaloPeer& P = peers[p];
+        if (P.peer < 0 || P.peer >= c->nccl_world || P.peer == c->nccl_rank || P.n_send < 0 || P.n_recv < 0 ||
+            (P.n_send && !P.send_ids) || (P.n_recv && !P.recv_ids))
+            return fail(c, SD_ERR_INVALID_ARG, "sd_halo_exchange: bad peer entry %d", p);
+        for (int i = 0; i < P.n_send; ++i) {
+            Slot* s = find(c, P.send_ids[i]);
+            if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", P.send_ids[i]);
+            if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps to send", P.send_ids[i]);
+            if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_main, s->ev_sd, 0));
+        }
+        for (int i = 0; i < P.n_recv; ++i) {
+            Slot* s = find(c, P.recv_ids[i]);
+            if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", P.recv_ids[i]);
+            CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
+            CU(c, wait_map_readers(c, s, c->s_main));
+            if (s->dn_pending) {
+                CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
+                s->dn_pending = false;
+            }
+        }
+    }
+    NC(c, api, api->group_start());
+    for (int p = 0; p < n_peers; ++p) {
+        const SdHaloPeer& P = peers[p];
+        for (int i = 0; i < P.n_send; ++i) {
+            Slot* s = find(c, P.send_ids[i]);
+            NC(c, api, api->send(s->depth, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
+            NC(c, api, api->send(s->sigma, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
+        }
+        for (int i = 0; i < P.n_recv; ++i) {
+            Slot* s = find(c, P.recv_ids[i]);
+            NC(c, api, api->recv(s->depth, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
+            NC(c, api, api->recv(s->sigma, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
+        }
+    }
+    NC(c, api, api->group_end());
+    for (int p = 0; p < n_peers; ++p) {
+        const SdHaloPeer& P = peers[p];
+        for (int i = 0; i < P.n_recv; ++i) {
+            Slot* s = find(c, P.recv_ids[i]);
+            CU(c, cudaEventRecord(s->ev_sd, c->s_main));
+            s->sd_recorded = true;
+            s->has_semidense = true;
+            s->has_checked = false;
+            s->has_points = false;
+            s->vlist_ok = false;
+        }
+        // the sends read our boundary maps on s_main: a later sd_semidense of those key frames (next pass) overwrites
+        // them on s_main as well, i.e. in stream order after the sends
+    }
+    return SD_OK;
+}
+
+int sd_semidense_loop(sd_ctx* c, const SdLoopItem* items, int n_items, int flags, int* inter_done) {
+    if (!c || n_items < 0 || (n_items > 0 && !items)) return fail(c, SD_ERR_INVALID_ARG, "sd_semidense_loop: bad argument");
+    // position of every item's key frame in the list, to find when an item's neighbours are all queued
+    std::unordered_map<int, int> pos;
+    pos.reserve((size_t)n_items * 2);
+    for (int i = 0; i < n_items; ++i) {
+        if (!items[i].nbr_ids || items[i].n < 1 || items[i].n > SD_MAX_NEIGHBOURS)
+            return fail(c, SD_ERR_INVALID_ARG, "sd_semidense_loop: item %d: bad neighbour list", i);
+        pos[items[i].kf_id] = i;
+    }
+    std::vector<int> ready_at(n_items, -1);  // index of the last item whose sd_semidense must be queued first; -2: skip
+    for (int i = 0; i < n_items; ++i) {
+        if (inter_done) inter_done[i] = 0;
+        int last = i;
+        for (int j = 0; (flags & SD_LOOP_INTERKF) && j < items[i].n && last != -2; ++j) {
+            auto it = pos.find(items[i].nbr_ids[j]);
+            if (it != pos.end()) last = std::max(last, it->second);
+            else {
+                Slot* nb = find(c, items[i].nbr_ids[j]);
+                if (!nb || !nb->has_semidense) last = -2;  // PM.cc:289-297: a neighbour without depth -> not checked in this pass
+            }
+        }
+        ready_at[i] = last;
+    }
+    auto finish = [&](int i) -> int {
+        const SdLoopItem& it = items[i];
+        if ((flags & SD_LOOP_INTERKF) && ready_at[i] != -2) {
+            int rc = sd_interkf_check_points(c, it.kf_id, it.nbr_ids, it.n);
+            if (rc != SD_OK) return rc;
+            if (inter_done) inter_done[i] = 1;
+        }
+        switch (it.download) {
+            case SD_DL_NONE: return SD_OK;
+            case SD_DL_DENSE: return sd_download_async(c, it.kf_id, it.out_depth, it.out_sigma, nullptr);
+            case SD_DL_DENSE_POINTS: return sd_download_async(c, it.kf_id, it.out_depth, it.out_sigma, it.out_points);
+            case SD_DL_COMPACT: return sd_download_compact_async(c, it.kf_id, 0, it.capacity, it.out_records, it.out_count);
+            case SD_DL_COMPACT_POINTS: return sd_download_compact_async(c, it.kf_id, 1, it.capacity, it.out_records, it.out_count);
+            default: return fail(c, SD_ERR_INVALID_ARG, "sd_semidense_loop: item %d: download mode %d", i, it.download);
+        }
+    };
+    // items in list order; the finishing stages of item j are queued right after the sd_semidense of the last item it
+    // waits for (so downloads and checks overlap the remaining searches); a pending pointer walks the list in order,
+    // like PM.cc:262's loop
+    std::vector<std::vector<int>> due(n_items);
+    std::vector<int> skipped;
+    for (int i = 0; i < n_items; ++i) {
+        if (ready_at[i] >= 0) due[ready_at[i]].push_back(i);
+        else skipped.push_back(i);
+    }
+    for (int k = 0; k < n_items; ++k) {
+        const SdLoopItem& it = items[k];
+        int rc = SD_OK;
+        if (!it.finish_only) rc = sd_semidense(c, it.kf_id, it.nbr_ids, it.nbr_rot_deg, it.n, it.min_invdepth, it.max_invdepth);
+        else if (!find(c, it.kf_id) || !find(c, it.kf_id)->has_semidense)
+            rc = fail(c, SD_ERR_NOT_READY, "sd_semidense_loop: item %d (key frame %d) is finish_only but has no maps", k, it.kf_id);
+        if (rc != SD_OK) return rc;
+        for (int i : due[k]) {
+            rc = finish(i);
+            if (rc != SD_OK) return rc;
+        }
+    }
+    for (int i : skipped) {  // no inter-key-frame stage in this pass; a requested download still delivers the intra maps
+        if (items[i].download == SD_DL_NONE || items[i].download == SD_DL_DENSE_POINTS || items[i].download == SD_DL_COMPACT_POINTS) continue;
+        int rc = finish(i);
+        if (rc != SD_OK) return rc;
+    }
+    return SD_OK;
+}
+
 int sd_export_maps(sd_ctx* c, int kf_id, float* depth_dev, float* sigma_dev) {
     if (!c || !depth_dev || !sigma_dev) return SD_ERR_INVALID_ARG;
     Slot* s = find(c, kf_id);
@@ -858,6 +1268,7 @@ int sd_export_maps(sd_ctx* c, int kf_id, float* depth_dev, float* sigma_dev) {
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     CU(c, cudaSetDevice(c->device));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
+    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
     CU(c, cudaMemcpy2DAsync(depth_dev, wb, s->depth, pb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     CU(c, cudaMemcpy2DAsync(sigma_dev, wb, s->sigma, pb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     return SD_OK;
@@ -866,6 +1277,7 @@ int sd_export_maps(sd_ctx* c, int kf_id, float* depth_dev, float* sigma_dev) {
 int sd_sync(sd_ctx* c) {
     if (!c) return SD_ERR_INVALID_ARG;
     CU(c, cudaSetDevice(c->device));
+    CU(c, poll_pack(c, true));
     CU(c, cudaStreamSynchronize(c->s_up));
     CU(c, cudaStreamSynchronize(c->s_srch));
     CU(c, cudaStreamSynchronize(c->s_main));
@@ -905,6 +1317,7 @@ int sd_span_begin(sd_ctx* c) {
 int sd_span_end(sd_ctx* c, double* ms) {
     if (!c || !ms) return SD_ERR_INVALID_ARG;
     CU(c, cudaSetDevice(c->device));
+    CU(c, poll_pack(c, true));  // the copies of pending compact downloads belong to the span
     CU(c, cudaEventRecord(c->ev_tmp, c->s_up));
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_tmp, 0));
     CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));

@@ -33,6 +33,7 @@ struct KfMeta {  // device-resident per key frame
     int active_count;          // entries in the active-pixel list
     unsigned int k1_task;      // next 32-entry task of the running k1_search launch (zeroed before each launch)
     int valid_count;           // entries in the valid-pixel list written by k23_intra (zeroed before each launch)
+    unsigned int k0_ticket;    // blocks of k0_gradient that have added their sums (the last one computes istddev)
 };
 
 struct NbrConst {  // per neighbour, warp-uniform, lives in kernel parameter (constant) space
@@ -82,8 +83,16 @@ struct IntraArgs {  // k23_intra: IntraKeyFrameDepthChecking + IntraKeyFrameDept
     float* depth_out;
     float* sigma_out;
     float* depth_copy;       // nullable: second copy of depth_out (the plane k4_inter_check patches)
-    uint32_t* vlist;         // nullable: compacted (y << 16 | x) of pixels with depth_out > 1e-6 inside the 2-px frame
+    uint32_t* vlist;         // nullable: compacted (y << 16 | x) of pixels with depth_out != 0 or sigma_out != 0 inside the 2-px frame
     int* vcount;             // nullable: entries in vlist (zeroed before the launch)
+};
+
+struct PointArgs {
+    int W, H, pitch_f;
+    float fx, fy, cx, cy;
+    float Twc[16];
+    const float* depth;
+    float* points;  // H x 3W, row pitch 3*W floats (tight)
 };
 
 struct InterNbr {
@@ -102,18 +111,12 @@ struct InterArgs {
     float chi_inter;  // smallest float >= 3.84
     const float* depth_in;
     float* depth_out;          // pre-filled with a copy of depth_in (k23_intra's depth_copy); patched at the listed pixels
-    const uint32_t* vlist;     // pixels to check: depth_in > 1e-6, inside the 2-px frame (PM.cc:659-662)
+    const uint32_t* vlist;     // pixels carrying a depth or a sigma inside the 2-px frame (PM.cc:659); depth_in <= 1e-6 is skipped (PM.cc:662)
     const int* vcount;
+    PointArgs P;               // k4_inter_check<true>: UpdateSemiDensePointSet (PM.cc:337-367) of the checked pixels, into a zeroed plane
     InterNbr nb[SD_MAX_NEIGHBOURS];
 };
 
-struct PointArgs {
-    int W, H, pitch_f;
-    float fx, fy, cx, cy;
-    float Twc[16];
-    const float* depth;
-    float* points;  // H x 3W, row pitch 3*W floats (tight)
-};
 
 // `d > 0.000001` with a float d and a double literal == `d > SD_EPS_F` (largest float <= 1e-6);
 // `d < 0.000001` == `d <= SD_EPS_F`.
@@ -312,18 +315,20 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
         block_base = tot ? atomicAdd(&meta->active_count, tot) : 0;
         atomicAdd(&meta->sum, a);
         atomicAdd(&meta->sumsq, b);
+        // the block that draws the last ticket sees every block's sums (fence before the ticket, atomic reads after):
+        // I_stddev = population standard deviation of the u8 image, double arithmetic (== cv::meanStdDev)
+        __threadfence();
+        if (atomicAdd(&meta->k0_ticket, 1u) == gridDim.x * gridDim.y - 1u) {
+            __threadfence();
+            const double n = (double)W * (double)H;
+            const double mean = (double)atomicAdd(&meta->sum, 0ull) / n;
+            const double var = (double)atomicAdd(&meta->sumsq, 0ull) / n - mean * mean;
+            meta->istddev = (float)sqrt(var > 0.0 ? var : 0.0);
+        }
     }
     __syncthreads();
     int pos = block_base + warp_cnt[ty] + incl - nact;
     for (int i = 0; i < nact; ++i) list[pos + i] = act[i];
-}
-
-// I_stddev = population standard deviation of the u8 image, double arithmetic (== cv::meanStdDev)
-__global__ void k0_finalize(KfMeta* meta, int W, int H) {
-    double n = (double)W * (double)H;
-    double mean = (double)meta->sum / n;
-    double var = (double)meta->sumsq / n - mean * mean;
-    meta->istddev = (float)sqrt(var > 0.0 ? var : 0.0);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -1144,7 +1149,9 @@ __global__ void __launch_bounds__(K23_THREADS) k23_intra(const IntraArgs A) {
             }
         }
         od[p] = dn; os[p] = sn;
-        if (inimg && x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2 && dn > SD_EPS_F) ventry[nvalid++] = ((uint32_t)y << 16) | (uint32_t)x;
+        // every pixel that carries anything: the ones k4_inter_check works on (depth > 1e-6, PM.cc:662) plus, for the
+        // compact download, the (in practice non-existent) ones with a depth in (0, 1e-6] or a sigma without a depth
+        if (inimg && x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2 && (dn != 0.0f || sn != 0.0f)) ventry[nvalid++] = ((uint32_t)y << 16) | (uint32_t)x;
     }
     if (y < A.H) {
         const size_t o = (size_t)y * A.pitch_out + xb;
@@ -1186,10 +1193,11 @@ __global__ void __launch_bounds__(K23_THREADS) k23_intra(const IntraArgs A) {
 }
 
 // valid-pixel list of a depth plane that did not come out of k23_intra (sd_import_maps)
-__global__ void __launch_bounds__(256) k_build_vlist(const float* __restrict__ depth, int pitch_f, int W, int H,
+__global__ void __launch_bounds__(256) k_build_vlist(const float* __restrict__ depth, const float* __restrict__ sigma, int pitch_f, int W, int H,
                                                      uint32_t* __restrict__ vlist, int* __restrict__ vcount) {
     const int x = blockIdx.x * 32 + (threadIdx.x & 31), y = blockIdx.y * 8 + (threadIdx.x >> 5);
-    const bool v = x >= 2 && x < W - 2 && y >= 2 && y < H - 2 && depth[(size_t)y * pitch_f + x] > SD_EPS_F;
+    const bool v = x >= 2 && x < W - 2 && y >= 2 && y < H - 2 &&
+                   (depth[(size_t)y * pitch_f + x] != 0.0f || sigma[(size_t)y * pitch_f + x] != 0.0f);
     const unsigned bal = __ballot_sync(0xffffffffu, v);
     int base = 0;
     if ((threadIdx.x & 31) == 0 && bal) base = atomicAdd(vcount, __popc(bal));
@@ -1209,6 +1217,19 @@ __global__ void __launch_bounds__(256) k_build_vlist(const float* __restrict__ d
 //    from a float estimate (relative error < 4e-7) unless it lies within 1e-5 of the threshold or an
 //    operand is tiny; then the double expression itself is evaluated.
 // ------------------------------------------------------------------------------------------------
+// world point of pixel (x, y) with inverse depth inv_d, PM.cc:349-363; zeros outside the 2-px frame or without depth
+__device__ __forceinline__ void backproject(const PointArgs& A, int x, int y, float inv_d, float& p0, float& p1, float& p2) {
+    p0 = p1 = p2 = 0.f;
+    if (x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2 && inv_d > SD_EPS_F) {
+        const float Z = 1 / inv_d;
+        const float X = Z * ((float)x - A.cx) / A.fx;
+        const float Y = Z * ((float)y - A.cy) / A.fy;
+        p0 = A.Twc[0] * X + A.Twc[1] * Y + A.Twc[2] * Z + A.Twc[3] * 1.0f;
+        p1 = A.Twc[4] * X + A.Twc[5] * Y + A.Twc[6] * Z + A.Twc[7] * 1.0f;
+        p2 = A.Twc[8] * X + A.Twc[9] * Y + A.Twc[10] * Z + A.Twc[11] * 1.0f;
+    }
+}
+
 struct K4Proj {  // projection of one pixel into one neighbour + the four depth taps, PM.cc:675-705
     bool inb;
     float rz, depthj;
@@ -1253,6 +1274,9 @@ __device__ __forceinline__ void k4_project(const InterArgs& A, const InterNbr& N
     }
 }
 
+// POINTS: also UpdateSemiDensePointSet (PM.cc:337-367, called right after the check at PM.cc:302-304) for the pixels
+// that keep a depth; the point plane was zeroed before the launch, which is what every other pixel gets (PM.cc:345-347).
+template <bool POINTS>
 __global__ void __launch_bounds__(128, K4_MIN_BLOCKS) k4_inter_check(const __grid_constant__ InterArgs A) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= *A.vcount) return;
@@ -1260,6 +1284,7 @@ __global__ void __launch_bounds__(128, K4_MIN_BLOCKS) k4_inter_check(const __gri
     const int px = (int)(ent & 0xffffu), py = (int)(ent >> 16);
     const size_t o = (size_t)py * A.pitch_f + px;
     const float depthp = A.depth_in[o];
+    if (!(depthp > SD_EPS_F)) return;  // PM.cc:662 (listed only because it carries a sigma)
     const float xp0 = ((float)px - A.cx) / A.fx, xp1 = ((float)py - A.cy) / A.fy;
     const float dp = 1 / depthp;
     // operator/(MatExpr, double): alpha = 1./s, which hal::gemm32f(float alpha) rounds to float
@@ -1317,24 +1342,55 @@ __global__ void __launch_bounds__(128, K4_MIN_BLOCKS) k4_inter_check(const __gri
         out = 1 / (dp + dpDelta);  // PM.cc:793
     }
     A.depth_out[o] = out;
+    if (POINTS) {
+        float p0, p1, p2;
+        backproject(A.P, px, py, out, p0, p1, p2);
+        if (out > SD_EPS_F) {
+            float* q = A.P.points + ((size_t)py * A.W + px) * 3;
+            q[0] = p0; q[1] = p1; q[2] = p2;
+        }
+    }
+}
+
+// Compact form of a key frame's results (sd_download_compact): one record per entry of the valid-pixel list --
+// SdCompactDepth {pixel = y << 16 | x, inverse depth, sigma} or SdCompactPoint {..., world point} -- in list order.
+struct PackArgs {
+    int W, pitch_f;
+    const uint32_t* vlist;
+    const int* vcount;
+    const float* depth;   // depth_checked when the inter-key-frame check ran, else the intra-key-frame map
+    const float* sigma;
+    const float* points;  // H x 3W (with_points)
+    int with_points;
+    uint8_t* out;         // cap records, 8-byte aligned
+    int* out_count;
+    int cap;
+};
+
+__global__ void __launch_bounds__(256) k7_pack(const PackArgs A) {
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    const int n = *A.vcount;
+    if (e == 0) *A.out_count = n;
+    if (e >= n || e >= A.cap) return;
+    const uint32_t ent = A.vlist[e];
+    const int px = (int)(ent & 0xffffu), py = (int)(ent >> 16);
+    const size_t o = (size_t)py * A.pitch_f + px;
+    const float d = __ldg(A.depth + o), s = __ldg(A.sigma + o);
+    if (A.with_points) {
+        const float* q = A.points + ((size_t)py * A.W + px) * 3;
+        uint2* r = reinterpret_cast<uint2*>(A.out + (size_t)e * sizeof(SdCompactPoint));
+        r[0] = make_uint2(ent, __float_as_uint(d));
+        r[1] = make_uint2(__float_as_uint(s), __float_as_uint(__ldg(q)));
+        r[2] = make_uint2(__float_as_uint(__ldg(q + 1)), __float_as_uint(__ldg(q + 2)));
+    } else {
+        uint32_t* r = reinterpret_cast<uint32_t*>(A.out + (size_t)e * sizeof(SdCompactDepth));
+        r[0] = ent; r[1] = __float_as_uint(d); r[2] = __float_as_uint(s);
+    }
 }
 
 // ------------------------------------------------------------------------------------------------
 // K5: UpdateSemiDensePointSet, PM.cc:337-367.  Twc*Pc: 4x4*4x1 small gemm, float left to right.
 // ------------------------------------------------------------------------------------------------
-// world point of pixel (x, y) with inverse depth inv_d, PM.cc:349-363; zeros outside the 2-px frame or without depth
-__device__ __forceinline__ void backproject(const PointArgs& A, int x, int y, float inv_d, float& p0, float& p1, float& p2) {
-    p0 = p1 = p2 = 0.f;
-    if (x >= 2 && x < A.W - 2 && y >= 2 && y < A.H - 2 && inv_d > SD_EPS_F) {
-        const float Z = 1 / inv_d;
-        const float X = Z * ((float)x - A.cx) / A.fx;
-        const float Y = Z * ((float)y - A.cy) / A.fy;
-        p0 = A.Twc[0] * X + A.Twc[1] * Y + A.Twc[2] * Z + A.Twc[3] * 1.0f;
-        p1 = A.Twc[4] * X + A.Twc[5] * Y + A.Twc[6] * Z + A.Twc[7] * 1.0f;
-        p2 = A.Twc[8] * X + A.Twc[9] * Y + A.Twc[10] * Z + A.Twc[11] * 1.0f;
-    }
-}
-
 // One block = 256 consecutive pixels of one row.  The 768 output floats are staged in shared memory so that the
 // global stores are whole float4s (a thread's own 3 floats would be a 12-byte-stride store).
 __global__ void __launch_bounds__(256) k5_pointset(const PointArgs A) {

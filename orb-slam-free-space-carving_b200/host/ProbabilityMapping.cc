@@ -3,9 +3,13 @@
 // Reference: /root/reference/src/Modeler/ProbabilityMapping.cc ("PM.cc").
 #include "ProbabilityMapping.h"
 
+#include <unistd.h>
+
 #include <algorithm>
 #include <cstdio>
+#include <cstring>
 #include <stdexcept>
+#include <unordered_set>
 
 namespace sdpm_host {
 
@@ -27,14 +31,105 @@ void ProbabilityMapping::check(int rc, const char* what) const {
     throw std::runtime_error(buf);
 }
 
+// ---- the worker thread, PM.cc:65-134 (finish handshake as in Modeler.cc:1441-1463) ----
+
+void ProbabilityMapping::Run() {
+    {
+        std::unique_lock<std::mutex> lock(mMutexFinish);
+        mbFinished = false;
+    }
+    while (1) {
+        if (CheckFinish()) break;  // PM.cc:69
+        SemiDenseLoop();           // PM.cc:76
+        UpdateAllSemiDensePointSet();  // PM.cc:79: make point positions follow the key-frame poses
+        usleep(5000);              // PM.cc:86
+    }
+    if (!obj_path_.empty()) SavePointCloudObj(obj_path_);  // PM.cc:99-130
+    SetFinish();  // PM.cc:134
+}
+
+void ProbabilityMapping::RunOnce() {
+    SemiDenseLoop();
+    UpdateAllSemiDensePointSet();
+}
+
+void ProbabilityMapping::RequestFinish() {
+    std::unique_lock<std::mutex> lock(mMutexFinish);
+    mbFinishRequested = true;
+}
+
+bool ProbabilityMapping::CheckFinish() {
+    std::unique_lock<std::mutex> lock(mMutexFinish);
+    return mbFinishRequested;
+}
+
+void ProbabilityMapping::SetFinish() {
+    std::unique_lock<std::mutex> lock(mMutexFinish);
+    mbFinished = true;
+}
+
+bool ProbabilityMapping::isFinished() {
+    std::unique_lock<std::mutex> lock(mMutexFinish);
+    return mbFinished;
+}
+
+// ---- residency ----
+
 // The reference keeps im_/GradImg/GradTheta/I_stddev in the KeyFrame; here they live in the
 // context, keyed by mnId, created on first use (image upload + gradient front end, kernel K0).
-void ProbabilityMapping::ensure_uploaded(KeyFrameView* kf) {
-    if (std::find(uploaded_.begin(), uploaded_.end(), kf->mnId) != uploaded_.end()) return;
-    if (kf->im_.empty()) throw std::invalid_argument("ProbabilityMapping: key frame without image");
-    check(sd_upload_keyframe(ctx_, kf->mnId, kf->im_.data, kf->im_.cols, kf->im_.rows, kf->im_.stride, kf->K, kf->Tcw),
-          "sd_upload_keyframe");
-    uploaded_.push_back(kf->mnId);
+// The reference reads GetRotation()/GetTranslation() at call time (PM.cc:638-644, 854-860, 973-979):
+// the pose the device holds is refreshed whenever the view's has moved.
+ProbabilityMapping::KfState& ProbabilityMapping::make_resident(KeyFrameView* kf) {
+    auto it = resident_.find(kf->mnId);
+    if (it == resident_.end()) {
+        if (kf->im_.empty()) throw std::invalid_argument("ProbabilityMapping: key frame without image");
+        check(sd_upload_keyframe(ctx_, kf->mnId, kf->im_.data, kf->im_.cols, kf->im_.rows, kf->im_.stride, kf->K, kf->Tcw),
+              "sd_upload_keyframe");
+        KfState st;
+        std::memcpy(st.Tcw, kf->Tcw, sizeof(st.Tcw));
+        it = resident_.emplace(kf->mnId, st).first;
+        const size_t px = (size_t)kf->im_.rows * kf->im_.cols;
+        if (kf->semidense_flag_ && kf->depth_map_.size() == px && kf->depth_sigma_.size() == px) {
+            // released earlier: its maps come back from the host members (checked depth once the inter-KF stage ran,
+            // which is what the reference's in-place depth_map_ holds)
+            check(sd_import_maps_host(ctx_, kf->mnId, kf->depth_map_.data(), kf->depth_sigma_.data()), "sd_import_maps_host");
+            it->second.imported = true;
+        }
+    } else if (std::memcmp(it->second.Tcw, kf->Tcw, sizeof(it->second.Tcw)) != 0) {
+        check(sd_set_pose(ctx_, kf->mnId, kf->Tcw), "sd_set_pose");
+        std::memcpy(it->second.Tcw, kf->Tcw, sizeof(it->second.Tcw));
+    }
+    return it->second;
+}
+
+void ProbabilityMapping::ReleaseKeyFrame(KeyFrameView* kf) {
+    auto it = resident_.find(kf->mnId);
+    if (it == resident_.end()) return;
+    check(sd_release_keyframe(ctx_, kf->mnId), "sd_release_keyframe");
+    resident_.erase(it);
+}
+
+void ProbabilityMapping::enforce_resident_limit(const std::vector<KeyFrameView*>& vpKFs) {
+    for (KeyFrameView* kf : vpKFs)
+        if (kf->isBad()) ReleaseKeyFrame(kf);
+    if (resident_limit_ == 0 || resident_.size() <= resident_limit_) return;
+    // key frames some unfinished key frame still needs: itself and its covisN picks
+    std::unordered_set<int> needed;
+    for (KeyFrameView* kf : vpKFs) {
+        if (kf->isBad() || kf->interKF_depth_flag_) continue;
+        needed.insert(kf->mnId);
+        for (KeyFrameView* nb : pick_neighbours(kf)) needed.insert(nb->mnId);
+        // neighbours that are not mapped yet will be picked later; keep what the full covisibility list names as well
+        for (size_t i = 0; i < kf->covisible.size() && (int)i < 2 * covis_n_; ++i) needed.insert(kf->covisible[i]->mnId);
+    }
+    std::vector<KeyFrameView*> cand;
+    for (KeyFrameView* kf : vpKFs)
+        if (kf->interKF_depth_flag_ && resident_.count(kf->mnId) && !needed.count(kf->mnId)) cand.push_back(kf);
+    std::sort(cand.begin(), cand.end(), [](const KeyFrameView* a, const KeyFrameView* b) { return a->mnId < b->mnId; });
+    for (KeyFrameView* kf : cand) {
+        if (resident_.size() <= resident_limit_) break;
+        ReleaseKeyFrame(kf);
+    }
 }
 
 // PM.cc:151-160 (and 278-287): the first covisN covisible key frames that are neither bad nor unmapped
@@ -50,16 +145,13 @@ std::vector<KeyFrameView*> ProbabilityMapping::pick_neighbours(KeyFrameView* kf)
     return closestMatches;
 }
 
-void ProbabilityMapping::Run() {
-    SemiDenseLoop();
-    UpdateAllSemiDensePointSet();
-}
-
 void ProbabilityMapping::SemiDenseLoop() {
     std::vector<KeyFrameView*> vpKFs = mpMap->GetAllKeyFrames();
-    // the images of every key frame first, so that the upload stream runs ahead of the compute stream
+    changed_.clear();
+    // the images of the key frames that will be reconstructed in this pass first, so that the upload stream runs ahead
+    // of the compute stream
     for (KeyFrameView* kf : vpKFs)
-        if (!kf->isBad()) ensure_uploaded(kf);
+        if (!kf->isBad() && !kf->semidense_flag_ && (int)pick_neighbours(kf).size() >= covis_n_) make_resident(kf);
     for (KeyFrameView* kf : vpKFs) SemiDenseRecon(kf);
 
     // PM.cc:262-313
@@ -73,13 +165,26 @@ void ProbabilityMapping::SemiDenseLoop() {
         for (size_t j = 0; j < neighbors.size(); j++)
             if (neighbors[j]->semidense_flag_) num_depth_kf++;
         if (num_depth_kf < covis_n_) continue;
-        InterKeyFrameDepthChecking(kf, neighbors);
-        UpdateSemiDensePointSet(kf);
+        // InterKeyFrameDepthChecking + UpdateSemiDensePointSet (PM.cc:302-304): one fused launch
+        std::vector<int> ids;
+        make_resident(kf);
+        for (KeyFrameView* n : neighbors) {
+            make_resident(n);
+            ids.push_back(n->mnId);
+        }
+        check(sd_interkf_check_points(ctx_, kf->mnId, ids.data(), (int)ids.size()), "sd_interkf_check_points");
+        kf->poseChanged = false;
         kf->interKF_depth_flag_ = true;
+        if (std::find(changed_.begin(), changed_.end(), kf) == changed_.end()) changed_.push_back(kf);
     }
-    // results back to the KeyFrame members, as the reference leaves them (PM.cc:225-226, 306, 361-363)
-    for (KeyFrameView* kf : vpKFs)
-        if (!kf->isBad() && kf->semidense_flag_) FetchResults(kf, kf->interKF_depth_flag_);
+    // results back to the KeyFrame members, as the reference leaves them (PM.cc:225-226, 306, 361-363): only what
+    // this pass produced
+    for (KeyFrameView* kf : changed_)
+        if (!kf->isBad()) FetchResults(kf, kf->interKF_depth_flag_);
+    changed_.clear();
+    enforce_resident_limit(vpKFs);
+    max_resident_seen_ = std::max(max_resident_seen_, resident_.size());
+    passes_++;
 }
 
 void ProbabilityMapping::SemiDenseRecon(KeyFrameView* kf) {
@@ -90,16 +195,17 @@ void ProbabilityMapping::SemiDenseRecon(KeyFrameView* kf) {
     std::vector<int> ids;
     std::vector<float> rots;
     for (KeyFrameView* kf2 : closestMatches) {  // PM.cc:170-179
-        ensure_uploaded(kf2);
+        make_resident(kf2);
         ids.push_back(kf2->mnId);
         rots.push_back(MedianRotInPlane(kf, kf2));
     }
     float max_depth, min_depth;
     StereoSearchConstraints(kf, &min_depth, &max_depth);  // PM.cc:184
-    ensure_uploaded(kf);
+    make_resident(kf).imported = false;
     // PM.cc:189-238: ComputeFundamental per neighbour, the pixel loop, the two intra-key-frame passes
     check(sd_semidense(ctx_, kf->mnId, ids.data(), rots.data(), (int)ids.size(), min_depth, max_depth), "sd_semidense");
     kf->semidense_flag_ = true;  // PM.cc:244
+    changed_.push_back(kf);
 }
 
 void ProbabilityMapping::StereoSearchConstraints(KeyFrameView* kf, float* min_depth, float* max_depth) {
@@ -126,8 +232,8 @@ float ProbabilityMapping::MedianRotInPlane(KeyFrameView* kf1, KeyFrameView* kf2)
 void ProbabilityMapping::EpipolarSearch(KeyFrameView* kf1, KeyFrameView* kf2, const int x, const int y, float /*pixel*/,
                                         float min_depth, float max_depth, depthHo* dh, const float* /*F12*/, float& best_u,
                                         float& best_v, float /*th_pi*/, float rot) {
-    ensure_uploaded(kf1);
-    ensure_uploaded(kf2);
+    make_resident(kf1);
+    make_resident(kf2);
     const int xy[2] = {x, y};
     float out[6] = {0, 0, -1, 0, 0, 0};
     check(sd_probe_epipolar(ctx_, kf1->mnId, kf2->mnId, xy, 1, min_depth, max_depth, rot, out), "sd_probe_epipolar");
@@ -183,12 +289,16 @@ void ProbabilityMapping::IntraKeyFrameDepthGrowing(PlaneView<float>& depth_map, 
 
 void ProbabilityMapping::InterKeyFrameDepthChecking(KeyFrameView* currentKf, std::vector<KeyFrameView*> neighbors) {
     std::vector<int> ids;
-    for (KeyFrameView* n : neighbors) ids.push_back(n->mnId);
+    make_resident(currentKf);
+    for (KeyFrameView* n : neighbors) {
+        make_resident(n);  // poses as they are now (PM.cc:638-644)
+        ids.push_back(n->mnId);
+    }
     check(sd_interkf_check(ctx_, currentKf->mnId, ids.data(), (int)ids.size()), "sd_interkf_check");
 }
 
 void ProbabilityMapping::UpdateSemiDensePointSet(KeyFrameView* kf) {
-    if (kf->poseChanged) check(sd_set_pose(ctx_, kf->mnId, kf->Tcw), "sd_set_pose");
+    make_resident(kf);  // uploads / re-installs if needed and pushes the current pose (PM.cc:340: GetPoseInverse at call time)
     check(sd_update_pointset(ctx_, kf->mnId), "sd_update_pointset");
     kf->poseChanged = false;  // PM.cc:331
 }
@@ -208,30 +318,76 @@ void ProbabilityMapping::UpdateAllSemiDensePointSet() {
 
 void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
     const size_t px = (size_t)kf->im_.rows * kf->im_.cols;
-    kf->depth_map_.resize(px);
-    kf->depth_sigma_.resize(px);
-    if (points) kf->SemiDensePointSets_.resize(3 * px);
-    check(sd_download(ctx_, kf->mnId, kf->depth_map_.data(), kf->depth_sigma_.data(),
-                      points ? kf->SemiDensePointSets_.data() : nullptr),
-          "sd_download");
+    auto st = resident_.find(kf->mnId);
+    if (st == resident_.end()) throw std::runtime_error("FetchResults: key frame is not resident on the device");
+    if (st->second.imported) {  // maps re-installed from the host: no compact form, dense planes
+        kf->depth_map_.resize(px);
+        kf->depth_sigma_.resize(px);
+        if (points) kf->SemiDensePointSets_.resize(3 * px);
+        check(sd_download(ctx_, kf->mnId, kf->depth_map_.data(), kf->depth_sigma_.data(),
+                          points ? kf->SemiDensePointSets_.data() : nullptr),
+              "sd_download");
+        filled_.erase(kf->mnId);
+        return;
+    }
+    // compact records over PCIe (about a quarter of the pixels carry anything), expanded into the dense members here
+    const int cap = (kf->im_.cols - 4) * (kf->im_.rows - 4);
+    if ((int)records_.size() < cap) records_.resize(cap);
+    int n = 0;
+    check(sd_download_compact(ctx_, kf->mnId, points ? 1 : 0, cap, records_.data(), &n), "sd_download_compact");
+    std::vector<uint32_t>& filled = filled_[kf->mnId];
+    const int W = kf->im_.cols;
+    const bool fresh_maps = kf->depth_map_.size() != px || kf->depth_sigma_.size() != px;
+    if (fresh_maps) {
+        kf->depth_map_.assign(px, 0.0f);
+        kf->depth_sigma_.assign(px, 0.0f);
+    }
+    const bool fresh_points = points && kf->SemiDensePointSets_.size() != 3 * px;
+    if (fresh_points) kf->SemiDensePointSets_.assign(3 * px, 0.0f);
+    const bool have_points = kf->SemiDensePointSets_.size() == 3 * px;
+    if (!fresh_maps || (have_points && !fresh_points)) {
+        for (uint32_t e : filled) {  // what the previous fetch wrote
+            const size_t o = (size_t)(e >> 16) * W + (e & 0xffffu);
+            kf->depth_map_[o] = 0.0f;
+            kf->depth_sigma_[o] = 0.0f;
+            if (have_points) { kf->SemiDensePointSets_[3 * o] = 0.0f; kf->SemiDensePointSets_[3 * o + 1] = 0.0f; kf->SemiDensePointSets_[3 * o + 2] = 0.0f; }
+        }
+    }
+    filled.resize(n);
+    if (points) {
+        const SdCompactPoint* r = records_.data();
+        for (int i = 0; i < n; ++i) {
+            const size_t o = (size_t)(r[i].pixel >> 16) * W + (r[i].pixel & 0xffffu);
+            kf->depth_map_[o] = r[i].depth;
+            kf->depth_sigma_[o] = r[i].sigma;
+            kf->SemiDensePointSets_[3 * o] = r[i].x; kf->SemiDensePointSets_[3 * o + 1] = r[i].y; kf->SemiDensePointSets_[3 * o + 2] = r[i].z;
+            filled[i] = r[i].pixel;
+        }
+    } else {
+        const SdCompactDepth* r = reinterpret_cast<const SdCompactDepth*>(records_.data());
+        for (int i = 0; i < n; ++i) {
+            const size_t o = (size_t)(r[i].pixel >> 16) * W + (r[i].pixel & 0xffffu);
+            kf->depth_map_[o] = r[i].depth;
+            kf->depth_sigma_[o] = r[i].sigma;
+            filled[i] = r[i].pixel;
+        }
+    }
 }
 
 int ProbabilityMapping::ConfidentPoints(KeyFrameView* kf, std::vector<Point3f>& out, double max_sigma, int max_points) {
-    if (kf->poseChanged) {  // PM.cc:329-331: points follow the current pose
-        check(sd_set_pose(ctx_, kf->mnId, kf->Tcw), "sd_set_pose");
-        kf->poseChanged = false;
-    }
-    const int npix = kf->im_.rows * kf->im_.cols;
-    int cap = (max_points > 0 && max_points < npix) ? max_points : 0, n = 0;
+    make_resident(kf);  // PM.cc:329-331: points follow the current pose
+    kf->poseChanged = false;
     static_assert(sizeof(Point3f) == 3 * sizeof(float), "Point3f must be three packed floats");
+    // the selection stays on the device; its size decides the host buffer, then one copy
+    const float *dx = nullptr, *ds = nullptr;
+    const uint32_t* dp = nullptr;
+    int n = 0;
+    check(sd_confident_points_device(ctx_, kf->mnId, max_sigma, max_points, &dx, &ds, &dp, &n, nullptr), "sd_confident_points_device");
+    if (n == 0) return 0;
     const size_t base = out.size();
-    if (cap == 0) {  // size the buffer to the selection: count first (device-resident result), then copy
-        check(sd_confident_points(ctx_, kf->mnId, max_sigma, max_points, 0, nullptr, nullptr, nullptr, &cap), "sd_confident_points");
-        if (cap == 0) return 0;
-    }
-    out.resize(base + (size_t)cap);
-    check(sd_confident_points(ctx_, kf->mnId, max_sigma, max_points, cap, &out[base].x, nullptr, nullptr, &n), "sd_confident_points");
-    if (n < cap) out.resize(base + (size_t)n);
+    out.resize(base + (size_t)n);
+    int got = 0;
+    check(sd_confident_points_fetch(ctx_, n, &out[base].x, nullptr, nullptr, &got), "sd_confident_points_fetch");
     return n;
 }
 

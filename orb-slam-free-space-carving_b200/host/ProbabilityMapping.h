@@ -9,15 +9,25 @@
 //   cv::Mat               ->  PlaneView<T>    (OpenCV C++ is not part of this build)
 //
 // Every method forwards to libsdpm.so; nothing here computes on the CPU what the reference
-// computes in its pixel loops.  The per-pixel methods (EpipolarSearch, GetSearchRange,
+// computes in its pixel loops (the one host loop is the expansion of the compact download records
+// into the dense depth_map_ / depth_sigma_ / SemiDensePointSets_ members: a scatter of values the
+// GPU produced).  The per-pixel methods (EpipolarSearch, GetSearchRange,
 // InverseDepthHypothesisFusion) are single-pixel probes that run the same device code as the
 // batch kernels.  Error convention: the reference's methods are `void` and return silently
 // (PM.cc:141-142, 160); here a failing C-ABI call throws std::runtime_error with sd_last_error().
+//
+// Threading: Run() is the reference's polling worker (PM.cc:65-134; the pattern of
+// Modeler::Run, Modeler.cc:51-98, started like System.cc:110-111) and is meant to own the object
+// from its own thread; RequestFinish() / isFinished() and Map::AddKeyFrame() are the only calls
+// another thread may make while it runs.
 #ifndef SDPM_HOST_PROBABILITYMAPPING_H
 #define SDPM_HOST_PROBABILITYMAPPING_H
 
+#include <atomic>
 #include <cstdint>
+#include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "sdpm.h"
@@ -53,27 +63,36 @@ struct KeyFrameView {
     PlaneView<const uint8_t> im_;  // kf->im_ / GetImage(), PM.cc:186
     float K[4] = {0, 0, 0, 0};     // fx, fy, cx, cy  (kf->fx ..., PM.cc:862-865; GetCalibrationMatrix, PM.cc:675)
     float Tcw[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};  // GetRotation / GetTranslation, PM.cc:885-888
-    bool bad = false;              // isBad()
-    bool mapped = true;            // Mapped(), PM.cc:156
+    std::atomic<bool> bad{false};     // isBad(); other SLAM threads flip these while the worker runs
+    std::atomic<bool> mapped{true};   // Mapped(), PM.cc:156
     std::vector<KeyFrameView*> covisible;  // GetVectorCovisibleKeyFrames(), best first, PM.cc:151
     std::vector<float> point_depths;       // GetAllPointDepths(), PM.cc:372
     std::vector<long long> map_points;     // GetMapPointMatches() as ids, < 0 = none, PM.cc:469-470
     std::vector<float> keypoint_angles;    // GetKeyPointsUn()[i].angle, PM.cc:477-478
     // results (host copies, W*H floats; point set H x 3W)
     std::vector<float> depth_map_, depth_sigma_, SemiDensePointSets_;
-    bool semidense_flag_ = false, interKF_depth_flag_ = false, poseChanged = false;
+    bool semidense_flag_ = false, interKF_depth_flag_ = false;
+    std::atomic<bool> poseChanged{false};
 
-    bool isBad() const { return bad; }
-    bool Mapped() const { return mapped; }
+    bool isBad() const { return bad.load(); }
+    bool Mapped() const { return mapped.load(); }
     void SetPose(const float Tcw_new[12]) {  // KeyFrame::SetPose + poseChanged (PM.cc:329)
         for (int i = 0; i < 12; ++i) Tcw[i] = Tcw_new[i];
         poseChanged = true;
     }
 };
 
-struct Map {  // ORB_SLAM2::Map::GetAllKeyFrames(), PM.cc:106, 322
+struct Map {  // ORB_SLAM2::Map: AddKeyFrame / GetAllKeyFrames under mMutexMap (Map.cc:36-40, 97-101), PM.cc:106, 322
     std::vector<KeyFrameView*> keyframes;
-    std::vector<KeyFrameView*> GetAllKeyFrames() const { return keyframes; }
+    mutable std::mutex mMutexMap;
+    void AddKeyFrame(KeyFrameView* kf) {
+        std::unique_lock<std::mutex> lock(mMutexMap);
+        keyframes.push_back(kf);
+    }
+    std::vector<KeyFrameView*> GetAllKeyFrames() const {
+        std::unique_lock<std::mutex> lock(mMutexMap);
+        return keyframes;
+    }
 };
 
 class ProbabilityMapping {
@@ -93,10 +112,18 @@ public:
     ProbabilityMapping(const ProbabilityMapping&) = delete;
     ProbabilityMapping& operator=(const ProbabilityMapping&) = delete;
 
-    // One iteration of the body of Run(), PM.cc:65-87: SemiDenseLoop + UpdateAllSemiDensePointSet.
+    // PM.cc:65-134: the worker.  while (!CheckFinish()) { SemiDenseLoop(); UpdateAllSemiDensePointSet(); usleep(5000); }
+    // then the .obj dump (PM.cc:99-130, skipped when the path is empty) and mbFinished = true.
     void Run();
+    void RequestFinish();  // the pattern of Modeler.cc:1441-1463
+    bool isFinished();
+    // One iteration of the body of Run(): SemiDenseLoop + UpdateAllSemiDensePointSet.
+    void RunOnce();
+    void SetPointCloudPath(const std::string& path) { obj_path_ = path; }  // default "semi_pointcloud.obj", PM.cc:99
+
     // PM.cc:137-318 over every key frame of the map: first half per key frame (SemiDenseRecon),
-    // then the inter-key-frame pass (PM.cc:262-313).
+    // then the inter-key-frame pass (PM.cc:262-313).  Only key frames whose results changed in this
+    // pass are copied back to their host members.
     void SemiDenseLoop();
     // PM.h:75 / PM.cc:137-257: one key frame, neighbour pick .. IntraKeyFrameDepthGrowing.
     void SemiDenseRecon(KeyFrameView* kf);
@@ -126,19 +153,45 @@ public:
     void ComputeFundamental(KeyFrameView* pKF1, KeyFrameView* pKF2, float F12[9]);
     float MedianRotInPlane(KeyFrameView* kf1, KeyFrameView* kf2);
 
-    // copy device results of a key frame into its host members (depth_map_, depth_sigma_, SemiDensePointSets_)
+    // copy device results of a key frame into its host members (depth_map_, depth_sigma_, SemiDensePointSets_):
+    // compact records over PCIe (sd_download_compact), expanded here
     void FetchResults(KeyFrameView* kf, bool points);
+    // Device memory of a live map: at most `n` key frames stay resident (0 = no limit).  After each pass the finished
+    // key frames (interKF_depth_flag_) that no unfinished key frame still lists among its covisN neighbours are released,
+    // oldest first, until the limit holds; bad key frames are released at once.  A released key frame that is needed
+    // again (a later key frame lists it, or its pose changes, PM.cc:321-334) is re-installed from its host members --
+    // then with the CHECKED inverse depth, which is what the reference's in-place depth_map_ holds by that time.
+    void SetResidentLimit(size_t n) { resident_limit_ = n; }
+    void ReleaseKeyFrame(KeyFrameView* kf);
+    size_t ResidentKeyFrames() const { return resident_.size(); }
+    size_t MaxResidentKeyFrames() const { return max_resident_seen_; }  // high-water mark after the release step of a pass
+    uint64_t Passes() const { return passes_.load(); }                  // completed SemiDenseLoop passes
     sd_ctx* context() const { return ctx_; }
 
 private:
-    void ensure_uploaded(KeyFrameView* kf);
+    struct KfState {
+        float Tcw[12];                 // the pose the device holds
+        bool imported = false;         // maps re-installed from the host members (no compact form)
+    };
+    bool CheckFinish();
+    void SetFinish();
+    KfState& make_resident(KeyFrameView* kf);  // upload on first use, push the pose if it moved, re-install released maps
     std::vector<KeyFrameView*> pick_neighbours(KeyFrameView* kf) const;  // PM.cc:151-160, 278-287
+    void enforce_resident_limit(const std::vector<KeyFrameView*>& vpKFs);
     void check(int rc, const char* what) const;
 
     Map* mpMap;
     sd_ctx* ctx_;
     int covis_n_;
-    std::vector<int> uploaded_;  // ids resident in the context
+    std::unordered_map<int, KfState> resident_;       // key frames with planes in the context, by mnId
+    std::unordered_map<int, std::vector<uint32_t>> filled_;  // by mnId: pixels of the host members the last FetchResults wrote
+    std::vector<KeyFrameView*> changed_;              // results to copy back at the end of the pass
+    std::vector<SdCompactPoint> records_;             // download scratch
+    size_t resident_limit_ = 0, max_resident_seen_ = 0;
+    std::atomic<uint64_t> passes_{0};
+    std::string obj_path_ = "semi_pointcloud.obj";
+    std::mutex mMutexFinish;
+    bool mbFinishRequested = false, mbFinished = false;
 };
 
 }  // namespace sdpm_host

@@ -2,7 +2,13 @@
 // tests/test_host_class.py, runs ProbabilityMapping::Run() through the class surface and writes the
 // KeyFrameView results back for the Python side to compare with the oracle.
 //
-//   test_pm_class <scene.bin> <out.bin> [obj path [max sigma]]   full run on cuda:0
+//   test_pm_class <scene.bin> <out.bin> [obj path [max sigma]]   one pass (RunOnce) over the whole map on cuda:0
+//   test_pm_class --stream[=limit] <scene.bin> <out.bin> [obj [max sigma]]
+//        replay stub of the live system: the worker thread runs ProbabilityMapping::Run() (PM.cc:65-134)
+//        while this thread inserts the recorded key frames one at a time, as LocalMapping does (LocalMapping.cc:94);
+//        `limit` > 0 bounds the key frames resident on the device (SetResidentLimit)
+//   test_pm_class --stale-pose <scene.bin> <out.bin>   uploads every key frame with a WRONG pose first, then SetPose(true
+//        pose) and one pass: the results must be those of the true poses (the reference reads poses at call time)
 //   test_pm_class --no-device-check                  exits 0 iff construction fails loudly without a GPU
 //
 // scene.bin (little endian): int32 nkf, w, h, covis_n; then per key frame:
@@ -11,11 +17,14 @@
 // then int32 nprobe; per probe: int32 kf1_index, kf2_index, x, y; float min_depth, max_depth, rot
 // out.bin: per key frame: int32 semidense_flag, interKF_flag; float depth[w*h], sigma[w*h]; int32 has_points;
 //   float points[3*w*h] if has_points; then per probe: float depth, sigma, best_u, best_v, supported, umin, umax
+#include <unistd.h>
+
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <stdexcept>
+#include <thread>
 #include <vector>
 
 #include "ProbabilityMapping.h"
@@ -49,8 +58,18 @@ int main(int argc, char** argv) {
         std::printf("a CUDA device is present: construction succeeded\n");
         return 0;
     }
+    bool stream = false, stale_pose = false;
+    long limit = 0;
+    if (argc >= 2 && !std::strncmp(argv[1], "--stream", 8)) {
+        stream = true;
+        if (argv[1][8] == '=') limit = std::atol(argv[1] + 9);
+        --argc; ++argv;
+    } else if (argc >= 2 && !std::strcmp(argv[1], "--stale-pose")) {
+        stale_pose = true;
+        --argc; ++argv;
+    }
     if (argc < 3) {
-        std::fprintf(stderr, "usage: %s scene.bin out.bin [cloud.obj]\n", argv[0]);
+        std::fprintf(stderr, "usage: %s [--stream[=limit] | --stale-pose] scene.bin out.bin [cloud.obj [max sigma]]\n", argv[0]);
         return 2;
     }
     try {
@@ -99,13 +118,47 @@ int main(int argc, char** argv) {
         std::fclose(f);
 
         Map map;
-        for (int i = 0; i < nkf; ++i) {
+        for (int i = 0; i < nkf; ++i)
             for (int c : cov[i]) kfs[i]->covisible.push_back(kfs[c].get());
-            map.keyframes.push_back(kfs[i].get());
-        }
 
         ProbabilityMapping pm(&map, 0, covis_n);
-        pm.Run();
+        if (stream) {
+            for (int i = 0; i < nkf; ++i) kfs[i]->mapped = false;
+            pm.SetResidentLimit((size_t)limit);
+            pm.SetPointCloudPath(argc >= 4 ? argv[3] : "");
+            std::thread worker([&pm] { pm.Run(); });  // started like mptModeler, System.cc:110-111
+            for (int i = 0; i < nkf; ++i) {
+                kfs[i]->mapped = true;
+                map.AddKeyFrame(kfs[i].get());
+                usleep(i % 3 == 0 ? 20000 : 1000);     // irregular arrival, several worker passes in between
+            }
+            const uint64_t p0 = pm.Passes();
+            while (pm.Passes() < p0 + 2) usleep(1000);  // two full passes after the last insertion
+            pm.RequestFinish();
+            worker.join();
+            if (!pm.isFinished()) throw std::runtime_error("worker did not set mbFinished");
+            std::printf("stream: %llu passes, resident %zu (max after release %zu, limit %ld)\n", (unsigned long long)pm.Passes(),
+                        pm.ResidentKeyFrames(), pm.MaxResidentKeyFrames(), limit);
+            if (limit > 0 && (long)pm.MaxResidentKeyFrames() > limit + 3 * covis_n + 1)
+                throw std::runtime_error("resident limit not enforced");
+        } else {
+            for (int i = 0; i < nkf; ++i) map.AddKeyFrame(kfs[i].get());
+            if (stale_pose) {
+                std::vector<std::vector<float>> truth(nkf);
+                for (int i = 0; i < nkf; ++i) {
+                    truth[i].assign(kfs[i]->Tcw, kfs[i]->Tcw + 12);
+                    kfs[i]->Tcw[3] += 0.07f + 0.01f * i;   // a wrong translation ...
+                    kfs[i]->Tcw[7] -= 0.03f;
+                }
+                for (int i = 0; i + 1 < nkf; ++i) {        // ... goes to the device with the upload a probe triggers
+                    ProbabilityMapping::depthHo dh;
+                    float bu = 0, bv = 0, F12[9] = {0};
+                    pm.EpipolarSearch(kfs[i].get(), kfs[i + 1].get(), w / 2, h / 2, 0.f, 1.2f, 0.8f, &dh, F12, bu, bv, 0.f, 0.f);
+                }
+                for (int i = 0; i < nkf; ++i) kfs[i]->SetPose(truth[i].data());   // BA / loop closing moved them
+            }
+            pm.RunOnce();
+        }
 
         std::FILE* o = std::fopen(argv[2], "wb");
         if (!o) throw std::runtime_error("cannot open output file");
@@ -132,7 +185,7 @@ int main(int argc, char** argv) {
             wr(o, rec, 7);
         }
         std::fclose(o);
-        if (argc >= 4 && !pm.SavePointCloudObj(argv[3], argc >= 5 ? std::atof(argv[4]) : 0.01)) return 1;
+        if (!stream && argc >= 4 && !pm.SavePointCloudObj(argv[3], argc >= 5 ? std::atof(argv[4]) : 0.01)) return 1;
         std::printf("ok: %d key frames %dx%d, covisN %d, %d probes\n", nkf, w, h, covis_n, (int)nprobe);
         return 0;
     } catch (const std::exception& e) {

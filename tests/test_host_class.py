@@ -78,10 +78,8 @@ def synth_roll(k):
     return _ROLL[k]
 
 
-@pytest.mark.gpu
-def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
-    scene = synth.Scene(SMALL_CAM, seed=21)
-    nkf, n = 12, 5
+def _host_scene(tmp_path, synth, pipeline, nkf=12, n=5, seed=21, with_probes=True):
+    scene = synth.Scene(SMALL_CAM, seed=seed)
     plan = pipeline.SequencePlan(scene, nkf, n)
     images = {k: scene.render(k) for k in plan.ids}
     # angles such that angle2 - angle1 == rot_in_plane(k1, k2) is not guaranteed in float; use what the
@@ -91,15 +89,18 @@ def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
     rots = {k: np.array([np.float32(np.float32(100.0) + np.float32(_ROLL[int(j)])) -
                          np.float32(np.float32(100.0) + np.float32(_ROLL[k])) for j in plan.nbrs[k]], np.float32)
             for k in plan.ids}
-    ys, xs = np.nonzero(np.abs(np.diff(images[plan.ids[4]].astype(np.int32), axis=1)) > 12)
-    mind, maxd = plan.prior[plan.ids[4]]
-    probes = [(4, 5, int(xs[i]) + 2, int(ys[i]), mind, maxd, 0.0) for i in range(0, len(xs), max(1, len(xs) // 40))][:40]
-    probes = [p for p in probes if 2 <= p[2] < scene.w - 2 and 2 <= p[3] < scene.h - 2]
-    scene_path, out_path, obj_path = tmp_path / "scene.bin", tmp_path / "out.bin", tmp_path / "cloud.obj"
+    probes = []
+    if with_probes:
+        ys, xs = np.nonzero(np.abs(np.diff(images[plan.ids[4]].astype(np.int32), axis=1)) > 12)
+        mind, maxd = plan.prior[plan.ids[4]]
+        probes = [(4, 5, int(xs[i]) + 2, int(ys[i]), mind, maxd, 0.0) for i in range(0, len(xs), max(1, len(xs) // 40))][:40]
+        probes = [p for p in probes if 2 <= p[2] < scene.w - 2 and 2 <= p[3] < scene.h - 2]
+    scene_path = tmp_path / "scene.bin"
     _write_scene(scene_path, scene, plan, images, n, probes, None)
-    r = subprocess.run([DRIVER, str(scene_path), str(out_path), str(obj_path), "0.05"], capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stdout + r.stderr
+    return scene, plan, images, rots, probes, scene_path
 
+
+def _oracle_run(po, scene, plan, images, rots):
     ora = po.Oracle(threads=po.lib().ora_max_threads())
     for k in plan.ids:
         ora.add_keyframe(k, images[k], scene.K, plan.poses[k])
@@ -108,14 +109,17 @@ def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
     for k in plan.ids:
         ora.interkf(k, plan.nbrs[k])
         ora.pointset(k)
+    return ora
 
+
+def _check_maps(raw, scene, plan, ora, po):
+    """The per-key-frame part of out.bin against the oracle, bit for bit; returns (offset, planes)."""
     px = scene.w * scene.h
-    raw = np.fromfile(out_path, np.uint8)
     off = 0
-    n_obj = 0
+    planes = {}
     for k in plan.ids:
         flags = raw[off:off + 8].view(np.int32); off += 8
-        assert list(flags) == [1, 1]
+        assert list(flags) == [1, 1], f"kf {k}: flags {list(flags)}"
         depth = raw[off:off + 4 * px].view(np.float32).reshape(scene.h, scene.w); off += 4 * px
         sigma = raw[off:off + 4 * px].view(np.float32).reshape(scene.h, scene.w); off += 4 * px
         hp = int(raw[off:off + 4].view(np.int32)[0]); off += 4
@@ -124,7 +128,20 @@ def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
         assert np.array_equal(depth, ora.plane(k, po.DEPTH_CHECKED)), f"depth kf {k}"
         assert np.array_equal(sigma, ora.plane(k, po.SIGMA)), f"sigma kf {k}"
         assert np.array_equal(pts, ora.plane(k, po.POINTS)), f"points kf {k}"
-        n_obj += int(((sigma.astype(np.float64) <= 0.05) & (depth > 0.000001)).sum())
+        planes[k] = (depth, sigma)
+    return off, planes
+
+
+@pytest.mark.gpu
+def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
+    scene, plan, images, rots, probes, scene_path = _host_scene(tmp_path, synth, pipeline)
+    out_path, obj_path = tmp_path / "out.bin", tmp_path / "cloud.obj"
+    r = subprocess.run([DRIVER, str(scene_path), str(out_path), str(obj_path), "0.05"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ora = _oracle_run(po, scene, plan, images, rots)
+    raw = np.fromfile(out_path, np.uint8)
+    off, planes = _check_maps(raw, scene, plan, ora, po)
+    n_obj = sum(int(((s.astype(np.float64) <= 0.05) & (d > 0.000001)).sum()) for d, s in planes.values())
     assert n_obj > 0
     with open(obj_path) as f:
         lines = f.read().splitlines()
@@ -147,6 +164,43 @@ def test_class_run_matches_oracle(tmp_path, pkg, po, synth, pipeline):
         assert (rec[5], rec[6]) == po.search_range(scene.K, R21, t21, scene.w, x, y, mind, maxd)
     assert off == raw.size
     assert nfound > 0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("limit", [0, 14])
+def test_class_streamed_equals_batch(tmp_path, pkg, po, synth, pipeline, limit):
+    """The replay stub of the live system (SURVEY 8f next-1): the worker thread runs ProbabilityMapping::Run()
+    (PM.cc:65-134) while key frames are inserted one at a time; the streamed result is the batch result, also when
+    only `limit` key frames may stay resident on the device (finished ones are released as the map grows)."""
+    scene, plan, images, rots, _, scene_path = _host_scene(tmp_path, synth, pipeline, nkf=24, n=5, seed=33, with_probes=False)
+    out_path, obj_path = tmp_path / "out.bin", tmp_path / "cloud.obj"
+    flag = "--stream" + (f"={limit}" if limit else "")
+    r = subprocess.run([DRIVER, flag, str(scene_path), str(out_path), str(obj_path)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "stream:" in r.stdout
+    ora = _oracle_run(po, scene, plan, images, rots)
+    raw = np.fromfile(out_path, np.uint8)
+    off, planes = _check_maps(raw, scene, plan, ora, po)
+    assert off == raw.size
+    # the worker wrote the reference's end-of-run dump (PM.cc:99-130, sigma <= 0.01)
+    n_obj = sum(int(((s.astype(np.float64) <= 0.01) & (d > 0.000001)).sum()) for d, s in planes.values())
+    with open(obj_path) as f:
+        assert len(f.read().splitlines()) == n_obj
+
+
+@pytest.mark.gpu
+def test_class_reads_poses_at_call_time(tmp_path, pkg, po, synth, pipeline):
+    """Key frames reach the device with a stale pose (uploaded before BA moved them); SetPose + one pass must give the
+    result of the CURRENT poses, as the reference reads GetRotation()/GetTranslation() at call time
+    (PM.cc:638-644, 854-860, 973-979)."""
+    scene, plan, images, rots, _, scene_path = _host_scene(tmp_path, synth, pipeline, with_probes=False)
+    out_path = tmp_path / "out.bin"
+    r = subprocess.run([DRIVER, "--stale-pose", str(scene_path), str(out_path)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ora = _oracle_run(po, scene, plan, images, rots)
+    raw = np.fromfile(out_path, np.uint8)
+    off, _ = _check_maps(raw, scene, plan, ora, po)
+    assert off == raw.size
 
 
 def _crafted_planes(rng, h, w, grow_case):
