@@ -8,25 +8,31 @@
 Workload (BASELINE.json configs[1]): 200 synthetic 1280x720 key frames (chris_logic_HD720
 intrinsics), 10 covisible neighbours, per GPU.  With N > 1 the sequence is N*200 key frames,
 sharded by contiguous index range, one rank per GPU, with one NCCL point-to-point exchange of the
-boundary (inverse depth, sigma) maps between the intra- and inter-key-frame stages (weak scaling).
+boundary (inverse depth, sigma) maps between the intra- and inter-key-frame stages (weak scaling);
+the exchange is the C ABI's own (sd_halo_exchange: grouped ncclSend / ncclRecv on the key-frame planes).
 
 One step = one pass of the whole path over the rank's key frames:
     K0 gradient front end -> K1 epipolar search + fusion -> K2/K3 intra checks -> [halo exchange]
-    -> K4 inter-key-frame check -> K5 point set.
-`value`  : inputs resident in HBM (device u8 images), results stay on the device.
-`e2e`    : the same through the C ABI with HOST buffers: pinned u8 images are copied host->device
-           and the (inverse depth, sigma) maps device->host inside the timed region, every step.
+    -> K4 inter-key-frame check + K5 point set (one launch).
+`value`      : inputs resident in HBM (device u8 images), results stay on the device.
+`e2e`        : the same through the C ABI with HOST buffers: pinned u8 images host->device and, device->host, the
+               compact form of both result maps (one {pixel, inverse depth, sigma} record per pixel that carries
+               anything; the consumer expands it: ProbabilityMapping::FetchResults) inside the timed region, every step.
+`e2e_points` : e2e with the world point of every record as well (all three reference outputs, PM.cc:225-226, 361-363).
+`e2e_dense`  : e2e with the two maps as dense planes (round 1's definition of e2e).
 Timing: CUDA events over all of the context's streams (sd_span_begin/end), barrier +
 torch.cuda.synchronize() on both sides, max over ranks.  L2: the working set per step (~5 GB)
 is far larger than the 126 MB L2, so no explicit flush is needed ("inputs_larger_than_l2").
+The timed legs run with per-kernel event timing OFF; `kernels_avg_us` / `roofline.avg_launch_us` come from one
+extra pass of the same step with it on (the context's streams overlap on purpose: a kernel's events then also span the
+time it shares the SMs with kernels of other key frames), `kernels_standalone_us` from one more pass with every stream
+drained before each kernel -- those are the durations the ncu launch list (profiles/) agrees with.
 
-`roofline` is quoted on stage K1 (k1_search + k1_fuse): `avg_launch_us` comes from the events of the timed region,
-where the context's streams overlap on purpose (a kernel's events then also span the time it shares the SMs with
-kernels of other key frames); `standalone_launch_us` / `kernels_standalone_us` come from one extra untimed pass with
-every stream drained before each kernel -- those are the durations the ncu launch list (profiles/) agrees with.
+With N > 1 every rank then checks its seam key frames (the owned key frames with neighbours on another rank) against the
+CPU oracle, bitwise, and the line carries `seam_parity` (the only driver-visible proof of the NCCL path).
 
 --impl reference times the reference's CPU algorithm for the path (the oracle port, all host
-threads) on a bounded sample of the same workload; rank 0 only.
+threads the process may use) on a bounded sample of the same workload; rank 0 only.
 """
 import argparse
 import importlib
@@ -56,8 +62,11 @@ def parse():
     ap.add_argument("--camera", default="720p")
     ap.add_argument("--nkf", type=int, default=200, help="key frames per GPU")
     ap.add_argument("--nbr", type=int, default=10, help="covisible neighbours")
+    ap.add_argument("--prior-sigmas", type=float, default=2.0, help="inverse-depth prior = mean +- s*sigma (PM.cc:381-382 uses 2)")
     ap.add_argument("--cpu-sample", type=int, default=12, help="key frames in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-configs", action="store_true", help="skip the short runs of BASELINE configs 1, 3, 5")
+    ap.add_argument("--no-seam-check", action="store_true")
     ap.add_argument("--seed", type=int, default=1234)
     return ap.parse_args()
 
@@ -67,12 +76,21 @@ def algorithmic_bytes_per_px(n):
     return {"grad": 9, "search": 17 + 9 * n, "intra": 16, "grow": 20, "inter": 8 + 8 * n, "points": 16}
 
 
-def measured_peak():
+def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
-            return float(json.load(f)["hbm_gbs"]), "measured"
+            d = json.load(f)
+        return float(d["hbm_gbs"]), "measured", float(d.get("sm_max_mhz", 1965.0))
     except Exception:
-        return 6650.0, "fallback"
+        return 6650.0, "fallback", 1965.0
+
+
+def host_cores():
+    """The CPUs this process may run on.  NOT omp_get_max_threads(): torchrun exports OMP_NUM_THREADS=1."""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
 
 
 class ClockSampler:
@@ -117,17 +135,53 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+def workload_name(args, world):
+    return (f"{args.nkf} synthetic {args.camera} key frames per GPU (chris_logic_HD720 intrinsics), "
+            f"{args.nbr} covisible neighbours" + (f", {world} ranks keyframe-sharded with NCCL map exchange" if world > 1 else ""))
+
+
+def config_block(args, world, W, H, extra=None):
+    """The keys both arms carry, so that the driver can tell they ran the same configuration."""
+    c = {"workload": workload_name(args, world), "camera": args.camera, "width": W, "height": H,
+         "neighbours": args.nbr, "keyframes_per_gpu": args.nkf, "prior_sigmas": args.prior_sigmas,
+         "l2": "inputs_larger_than_l2",
+         "parallelism": f"keyframe-shard x{world}" if world > 1 else "single GPU"}
+    c.update(extra or {})
+    return c
+
+
+# ------------------------------------------------------------------------------------------------
+# host-side inputs of a key-frame range (what ORB-SLAM's map would provide), without the product library:
+# the reference arm and the seam check build them with the oracle's own StereoSearchConstraints
+# ------------------------------------------------------------------------------------------------
+class HostPlan:
+    def __init__(self, synth, scene, total_kf, n, ids, prior_fn, prior_sigmas=2.0):
+        self.scene, self.ids = scene, list(ids)
+        self.poses, self.nbrs, self.rots, self.prior = {}, {}, {}, {}
+        for k in self.ids:
+            self.add(synth, total_kf, n, k, prior_fn, prior_sigmas)
+
+    def add(self, synth, total_kf, n, k, prior_fn, prior_sigmas=2.0):
+        if k in self.nbrs:
+            return
+        scene = self.scene
+        self.poses[k] = scene.pose(k)
+        nb = synth.Scene.neighbours(k, total_kf, n)
+        self.nbrs[k] = nb.astype(np.int32)
+        self.rots[k] = np.array([synth.Scene.rot_in_plane(k, int(j)) for j in nb], np.float32)
+        d = scene.sparse_depths(k, 1000)
+        if prior_sigmas == 2.0:
+            self.prior[k] = prior_fn(d)                      # PM.cc:370-383 verbatim
+        else:                                                # BASELINE config 5: widened prior
+            mean, sd = float(np.mean(d)), float(np.std(d))
+            self.prior[k] = (float(np.float32(1.0 / (mean - prior_sigmas * sd))), float(np.float32(1.0 / (mean + prior_sigmas * sd))))
+
+
 # ------------------------------------------------------------------------------------------------
 # reference arm / CPU baseline: the oracle port on the host cores
 # ------------------------------------------------------------------------------------------------
-def cpu_pass(po, synth, pipeline, args, sample_kf, images=None, plan=None):
-    """One pass of the whole path (front end .. point set) over `sample_kf` key frames with the
-    CPU oracle on all host threads; returns (seconds, plan, images)."""
-    if plan is None:
-        scene = synth.Scene(args.camera, seed=args.seed)
-        plan = pipeline.SequencePlan(scene, sample_kf, min(args.nbr, sample_kf - 1))
-        images = {k: scene.render(k) for k in plan.ids}
-    threads = po.lib().ora_max_threads()
+def cpu_pass(po, plan, images, threads):
+    """One pass of the whole path (front end .. point set) over the plan's key frames with the CPU oracle."""
     t0 = time.perf_counter()
     ora = po.Oracle(threads=threads)
     for k in plan.ids:
@@ -139,39 +193,49 @@ def cpu_pass(po, synth, pipeline, args, sample_kf, images=None, plan=None):
         ora.pointset(k)
     dt = time.perf_counter() - t0
     ora.close()
-    return dt, plan, images, threads
+    return dt
 
 
-def workload_name(args, world):
-    return (f"{args.nkf} synthetic {args.camera} key frames per GPU (chris_logic_HD720 intrinsics), "
-            f"{args.nbr} covisible neighbours" + (f", {world} ranks keyframe-sharded with NCCL map exchange" if world > 1 else ""))
+def cpu_sample_plan(args, synth, po, sample):
+    scene = synth.Scene(args.camera, seed=args.seed)
+    plan = HostPlan(synth, scene, sample, min(args.nbr, sample - 1), range(sample), po.stereo_search_constraints, args.prior_sigmas)
+    images = {k: scene.render(k) for k in plan.ids}
+    return scene, plan, images
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    load_package()
+    load_package()                                   # module import only: the product library is never dlopen'ed in this arm
     synth = importlib.import_module(PKG_NAME + ".synth")
-    pipeline = importlib.import_module(PKG_NAME + ".pipeline")
     from oracle import pm_oracle as po
+    threads = host_cores()
     sample = max(args.cpu_sample, args.nbr + 1)
-    _, plan, images, threads = cpu_pass(po, synth, pipeline, args, sample)   # also warms caches / builds
-    for _ in range(max(args.warmup - 1, 0)):
-        cpu_pass(po, synth, pipeline, args, sample, images, plan)
+    scene, plan, images = cpu_sample_plan(args, synth, po, sample)
+    for _ in range(max(args.warmup, 1)):
+        cpu_pass(po, plan, images, threads)
     t = 0.0
     for _ in range(args.steps):
-        t += cpu_pass(po, synth, pipeline, args, sample, images, plan)[0]
+        t += cpu_pass(po, plan, images, threads)
     kfps = sample * args.steps / t
+    # "as shipped": the reference builds without -fopenmp -> one thread; one pass over the smallest sample that
+    # still has args.nbr neighbours per key frame
+    s1 = args.nbr + 1
+    _, plan1, images1 = cpu_sample_plan(args, synth, po, s1) if s1 != sample else (scene, plan, images)
+    dt1 = cpu_pass(po, plan1, images1, 1)
     line = {
         "impl": "reference", "metric": METRIC, "value": kfps, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": workload_name(args, 1), "camera": args.camera, "neighbours": args.nbr},
+        "config": config_block(args, max(args.gpus, 1), scene.w, scene.h),
+        "sample_keyframes_per_step": sample,
         "cpu_baseline": {"value": kfps, "unit": UNIT, "cores": threads, "kind": "port",
                          "sample": f"{sample} of the {args.nkf} key frames per step, all stages K0..K5, OpenMP on the reference's five pragma loops"},
+        "cpu_baseline_1thread": {"value": s1 / dt1, "unit": UNIT, "cores": 1, "kind": "port",
+                                 "sample": f"{s1} key frames, one pass ({dt1:.1f} s): the reference as shipped builds without OpenMP (SURVEY F4)"},
         "e2e": {"value": kfps, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "pixels_per_s": kfps * plan.scene.w * plan.scene.h,
+        "pixels_per_s": kfps * scene.w * scene.h,
         "note": "reference CPU algorithm = oracle/pm_oracle.cc (PM.cc is not compilable: SURVEY F1-F3); per-call cv::Mat churn hoisted, so faster than the literal reference",
     }
     emit(line)
@@ -206,6 +270,103 @@ def bind_to_gpu_numa_node(torch, local):
     return None
 
 
+LEGS = ("value", "e2e", "e2e_points", "e2e_dense")
+
+
+class Workload:
+    """One rank's share of a key-frame sequence, resident inputs, pinned staging and the marshalled C calls of a step."""
+
+    def __init__(self, torch, pkg, synth, sharding, ctx, dev, camera, nkf_per_rank, n, world, rank, seed, prior_sigmas=2.0,
+                 legs=LEGS, record_fill=0.42):
+        self.torch, self.pkg, self.ctx, self.world, self.rank, self.n = torch, pkg, ctx, world, rank, n
+        self.total_kf = nkf_per_rank * world
+        scene = self.scene = synth.Scene(camera, seed=seed)
+        W, H = self.W, self.H = scene.w, scene.h
+        nbr_of = lambda k: synth.Scene.neighbours(k, self.total_kf, n)
+        shard = self.shard = sharding.make_plan(self.total_kf, world, rank, nbr_of)
+        self.owned, self.resident = shard.owned, shard.resident
+        self.plan = HostPlan(synth, scene, self.total_kf, n, self.owned, pkg.stereo_search_constraints, prior_sigmas)
+        self.poses = {k: scene.pose(k) for k in self.resident}
+        # inputs: pinned host images (e2e legs) and a device-resident copy (value leg)
+        self.host_img = torch.empty((len(self.resident), H, W), dtype=torch.uint8).pin_memory()
+        hnp = self.host_img.numpy()
+        for i, k in enumerate(self.resident):
+            scene.render(k, out=hnp[i])
+        self.dev_img = self.host_img.to(dev)
+        self.slot = {k: i for i, k in enumerate(self.resident)}
+        # outputs: ONE pinned staging area, viewed per leg (dense planes / compact records)
+        px = W * H
+        self.cap = int(record_fill * px)              # records per key frame the staging area holds (about 26 % carry anything)
+        per_kf = max(2 * px * 4, self.cap * pkg.COMPACT_POINT.itemsize)
+        self.out = torch.empty((len(self.owned), per_kf), dtype=torch.uint8).pin_memory()
+        self.counts = torch.zeros((len(self.owned),), dtype=torch.int32).pin_memory()
+        self.oslot = {k: i for i, k in enumerate(self.owned)}
+        self.halo = ctx.make_halo(shard.send, shard.recv) if world > 1 else None
+        self.loops = {leg: self._make_loops(leg) for leg in legs}
+
+    def _download(self, leg, k):
+        pkg, i = self.pkg, self.oslot[k]
+        base = self.out[i].data_ptr()
+        if leg == "value":
+            return None
+        if leg == "e2e":
+            return (pkg.SD_DL_COMPACT, base, self.cap, self.counts[i:].data_ptr())
+        if leg == "e2e_points":
+            return (pkg.SD_DL_COMPACT_POINTS, base, self.cap, self.counts[i:].data_ptr())
+        return (pkg.SD_DL_DENSE, base, base + self.W * self.H * 4)
+
+    def _item(self, leg, k, finish_only=False, download=True):
+        p = self.plan
+        return dict(kf_id=k, nbrs=p.nbrs[k], rots=p.rots[k], prior=p.prior[k], finish_only=finish_only,
+                    download=self._download(leg, k) if download else None)
+
+    def _make_loops(self, leg):
+        """world == 1: one sd_semidense_loop over the owned key frames.  world > 1: the boundary key frames first (the
+        ones some peer needs), the exchange, then the boundary key frames' finishing stages + the interior."""
+        ctx = self.ctx
+        if self.world == 1:
+            return [("loop", ctx.make_loop([self._item(leg, k) for k in self.owned]))]
+        boundary = sorted({k for ids in self.shard.send.values() for k in ids})
+        bset = set(boundary)
+        interior = [k for k in self.owned if k not in bset]
+        ops = [("loop", ctx.make_loop([self._item(leg, k, download=False) for k in boundary], interkf=False)),
+               ("exchange", None),
+               ("loop", ctx.make_loop([self._item(leg, k, finish_only=True) for k in boundary] + [self._item(leg, k) for k in interior]))]
+        return ops
+
+    def step(self, leg):
+        ctx, W, H, K = self.ctx, self.W, self.H, self.scene.K
+        src, on_dev = (self.dev_img, True) if leg == "value" else (self.host_img, False)
+        for k in self.resident:
+            ctx.upload_keyframe_ptr(k, src[self.slot[k]].data_ptr(), W, H, W, K, self.poses[k], device=on_dev)
+        for op, arg in self.loops[leg]:
+            if op == "loop":
+                done = ctx.semidense_loop(arg)
+                if arg["flags"] and not done.all():
+                    raise RuntimeError("sd_semidense_loop skipped an inter-key-frame check")
+            elif not os.environ.get("BENCH_SKIP_NCCL"):
+                ctx.halo_exchange(self.halo)
+
+    def bytes_per_step(self, leg):
+        px = self.W * self.H
+        h2d = 0 if leg == "value" else len(self.resident) * px
+        if leg == "value":
+            d2h = 0
+        elif leg == "e2e_dense":
+            d2h = len(self.owned) * 2 * px * 4
+        else:
+            rec = self.pkg.COMPACT_POINT.itemsize if leg == "e2e_points" else self.pkg.COMPACT_DEPTH.itemsize
+            d2h = int(self.counts.numpy().astype(np.int64).sum()) * rec + 4 * len(self.owned)
+        return h2d, d2h
+
+    def records(self, leg, k):
+        i = self.oslot[k]
+        n = int(self.counts[i])
+        if n > self.cap:
+            raise RuntimeError(f"key frame {k}: {n} records exceed the staging capacity {self.cap}")
+        dt = self.pkg.COMPACT_POINT if leg == "e2e_points" else self.pkg.COMPACT_DEPTH
+        return self.out[i].numpy()[:n * dt.itemsize].view(dt)
+
 
 def run_b200(args):
     import torch
@@ -223,173 +384,89 @@ def run_b200(args):
 
     pkg = load_package()
     synth = importlib.import_module(PKG_NAME + ".synth")
-    pipeline = importlib.import_module(PKG_NAME + ".pipeline")
     sharding = importlib.import_module(PKG_NAME + ".sharding")
 
-    n = args.nbr
-    total_kf = args.nkf * world
-    scene = synth.Scene(args.camera, seed=args.seed)
-    W, H = scene.w, scene.h
-    gplan = pipeline.SequencePlan(scene, total_kf, n) if world == 1 else None
-    nbr_of = (lambda k: gplan.nbrs[k]) if gplan else (lambda k: synth.Scene.neighbours(k, total_kf, n))
-    shard = sharding.make_plan(total_kf, world, rank, nbr_of)
-    owned, resident = shard.owned, shard.resident
-    if gplan is None:  # host-side inputs for the owned key frames only
-        class P:  # minimal stand-in for SequencePlan restricted to this rank
-            pass
-        gplan = P()
-        gplan.scene = scene
-        gplan.poses = {k: scene.pose(k) for k in resident}
-        gplan.nbrs = {k: nbr_of(k).astype(np.int32) for k in owned}
-        gplan.rots = {k: np.array([synth.Scene.rot_in_plane(k, j) for j in gplan.nbrs[k]], np.float32) for k in owned}
-        gplan.prior = {k: pkg.stereo_search_constraints(scene.sparse_depths(k, 1000)) for k in owned}
-
-    # inputs: pinned host images (e2e leg) and a device-resident copy (value leg)
-    host_img = torch.empty((len(resident), H, W), dtype=torch.uint8).pin_memory()
-    hnp = host_img.numpy()
-    for i, k in enumerate(resident):
-        scene.render(k, out=hnp[i])
-    dev_img = host_img.to(dev)
-    slot = {k: i for i, k in enumerate(resident)}
-    host_out = torch.empty((len(owned), 2, H, W), dtype=torch.float32).pin_memory()
-    oslot = {k: i for i, k in enumerate(owned)}
-    img_bytes = W * H
-
     ctx = pkg.Context(local)
-    ext = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
-    send_buf = {p: torch.empty((len(ids), 2, H, W), dtype=torch.float32, device=dev) for p, ids in shard.send.items()}
-    recv_buf = {p: torch.empty((len(ids), 2, H, W), dtype=torch.float32, device=dev) for p, ids in shard.recv.items()}
-
-    def pack(ids, peer):
-        t = send_buf[peer]
-        for i, k in enumerate(ids):
-            ctx.export_maps(k, t[i, 0].data_ptr(), t[i, 1].data_ptr())
-        return t
-
-    def exchange():
-        if world == 1:
-            return 0
-        if os.environ.get("BENCH_SKIP_NCCL"):   # diagnostic: same packing / installing, no wire (results are then wrong at the seams)
-            for p, ids in shard.send.items():
-                pack(ids, p)
-            for p, ids in shard.recv.items():
-                for i, k in enumerate(ids):
-                    ctx.import_maps(k, recv_buf[p][i, 0].data_ptr(), recv_buf[p][i, 1].data_ptr())
-            return 0
-        with torch.cuda.stream(ext):  # NCCL orders against the context's compute stream
-            ops = []
-            for p in sorted(set(shard.send) | set(shard.recv)):
-                if p in shard.send:
-                    ops.append(dist.P2POp(dist.isend, pack(shard.send[p], p), p))
-                if p in shard.recv:
-                    ops.append(dist.P2POp(dist.irecv, recv_buf[p], p))
-            for r in dist.batch_isend_irecv(ops):
-                r.wait()
-            for p, ids in shard.recv.items():
-                for i, k in enumerate(ids):
-                    ctx.import_maps(k, recv_buf[p][i, 0].data_ptr(), recv_buf[p][i, 1].data_ptr())
-        return sum(t.numel() * 4 for t in list(send_buf.values()) + list(recv_buf.values()))
-
-    last_needed = {k: int(max(gplan.nbrs[k].max(), k)) for k in owned}
-    schedule = sharding.pipelined_schedule(shard, lambda k: gplan.nbrs[k]) if world > 1 else None
-    plain_schedule = [("semidense", k) for k in owned] + [("exchange",)] + [("finish", k) for k in owned]
-
-    def step(e2e):
-        for k in resident:
-            if e2e:
-                ctx.upload_keyframe_ptr(k, host_img[slot[k]].data_ptr(), W, H, W, scene.K, gplan.poses[k])
-            else:
-                ctx.upload_keyframe_ptr(k, dev_img[slot[k]].data_ptr(), W, H, W, scene.K, gplan.poses[k], device=True)
-
-        def finish(j):
-            ctx.interkf_check(j, gplan.nbrs[j])
-            ctx.update_pointset(j)
-            if e2e:
-                ctx.download_async_ptr(j, host_out[oslot[j], 0].data_ptr(), host_out[oslot[j], 1].data_ptr())
-
-        if world == 1:
-            # software pipeline: the inter-KF check of key frame j is issued as soon as every neighbour
-            # of j has its intra-KF maps queued, so downloads overlap the remaining search kernels
-            pending = list(owned)
-            for k in owned:
-                mn, mx = gplan.prior[k]
-                ctx.semidense(k, gplan.nbrs[k], gplan.rots[k], mn, mx)
-                while pending and last_needed[pending[0]] <= k:
-                    finish(pending.pop(0))
-            for j in pending:
-                finish(j)
-        else:
-            # boundary key frames first, one exchange, then the interior with the same software pipeline
-            # (sharding.pipelined_schedule): only the few key frames with halo neighbours wait for the peers
-            for op in (plain_schedule if os.environ.get("BENCH_PLAIN_SCHEDULE") else schedule):
-                if op[0] == "semidense":
-                    k = op[1]
-                    mn, mx = gplan.prior[k]
-                    ctx.semidense(k, gplan.nbrs[k], gplan.rots[k], mn, mx)
-                elif op[0] == "exchange":
-                    exchange()
-                else:
-                    finish(op[1])
+    if world > 1:   # the path's own communicator: rank 0 draws the id, torch.distributed only carries the 128 bytes
+        ids = [pkg.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, device=dev)
+        ctx.comm_init(world, rank, ids[0])
+    wl = Workload(torch, pkg, synth, sharding, ctx, dev, args.camera, args.nkf, args.nbr, world, rank, args.seed, args.prior_sigmas)
+    W, H, n = wl.W, wl.H, args.nbr
 
     def barrier():
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    host_issue_ms = []
+    host_issue_ms = {}
 
-    def timed(e2e, steps, warmup, sampler=None):
+    def timed(work, leg, steps, warmup, sampler=None):
+        c = work.ctx
         for _ in range(warmup):
-            step(e2e)
-            ctx.sync()
+            work.step(leg)
+            c.sync()
         barrier()
         if sampler:
             sampler.start()
-        ctx.timing_reset()
-        l0 = ctx.launch_count()
-        ctx.span_begin()
+        l0 = c.launch_count()
+        c.span_begin()
         t_host = time.perf_counter()
         for _ in range(steps):
-            step(e2e)
-        host_issue_ms.append(1e3 * (time.perf_counter() - t_host))   # host time to ISSUE the steps (no device wait)
-        ms = ctx.span_end()
+            work.step(leg)
+        host_issue_ms[leg] = 1e3 * (time.perf_counter() - t_host) / steps   # host time to ISSUE a step (no device wait)
+        ms = c.span_end()
         barrier()
         clocks = sampler.stop() if sampler else None
-        launches = ctx.launch_count() - l0
+        launches = c.launch_count() - l0
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         if os.environ.get("BENCH_VERBOSE"):
-            sys.stderr.write(f"rank {rank}: numa cpus {numa}; span {ms:.2f} ms for {steps} steps, host issue {host_issue_ms[-1]:.2f} ms\n")
+            sys.stderr.write(f"rank {rank}: numa cpus {numa}; {leg}: span {ms:.2f} ms for {steps} steps, host issue {host_issue_ms[leg]:.2f} ms/step\n")
         if world > 1:
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), launches, clocks
 
-    ctx.timing_enable(True)
     sampler = ClockSampler(local) if rank == 0 else None
-    ms_v, launches, clocks = timed(False, args.steps, args.warmup, sampler)
-    kt = ctx.timing()
-    ctx.timing_enable(False)
-    ms_e, _, _ = timed(True, args.steps, max(args.warmup, 1))
+    ms, launches, clocks, bytes_ps = {}, {}, None, {}
+    for leg in LEGS:
+        ms[leg], launches[leg], ck = timed(wl, leg, args.steps, args.warmup if leg == "value" else max(min(args.warmup, 2), 1),
+                                           sampler if leg == "value" else None)
+        clocks = clocks or ck
+        bytes_ps[leg] = wl.bytes_per_step(leg)
+        if leg in ("e2e", "e2e_points"):   # the records that came back are real results: expand one key frame, compare with the planes
+            k = wl.owned[len(wl.owned) // 2]
+            got = pkg.expand_compact(wl.records(leg, k), H, W, points=leg == "e2e_points")
+            ref = ctx.download(k, points=leg == "e2e_points")
+            if not all(np.array_equal(a, b) for a, b in zip(got, ref)):
+                raise RuntimeError(f"{leg}: compact records of key frame {k} do not expand to the dense planes")
+            for kk in wl.owned:
+                wl.records(leg, kk)        # raises if a count exceeded the staging capacity
+    valid_fraction = float((ctx.download(wl.owned[len(wl.owned) // 2])[0] > 1e-6).mean())
 
-    # standalone kernel durations: one more untimed pass with every stream drained before each kernel, so a launch's
-    # events bracket that kernel alone.  In the timed region the five streams overlap on purpose; there the events
-    # of a kernel also span the time it shares the SMs with (or waits behind) kernels of other key frames.
+    # per-kernel durations: one more pass of the same step with event timing on, then one with every stream drained
+    # before each kernel (stand-alone durations)
+    ctx.timing_enable(True)
+    ctx.timing_reset()
+    wl.step("value")
+    ctx.sync()
+    kt = ctx.timing()
     ctx.timing_enable(True, serial=True)
     ctx.timing_reset()
-    step(False)
+    wl.step("value")
     ctx.sync()
     kt_alone = ctx.timing()
     ctx.timing_enable(False)
 
     kf_total_per_step = args.nkf * world
-    value = kf_total_per_step * args.steps / (ms_v * 1e-3)
-    e2e = kf_total_per_step * args.steps / (ms_e * 1e-3)
+    rate = {leg: kf_total_per_step * args.steps / (ms[leg] * 1e-3) for leg in LEGS}
 
-    # sanity: the maps that came back are real results
-    d = host_out[len(owned) // 2, 0].numpy()
-    valid_fraction = float((d > 1e-6).mean())
+    seam = None
+    if world > 1 and not args.no_seam_check:
+        seam = seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank)
 
+    line = None
     if rank == 0:
-        peak, peak_src = measured_peak()
+        peak, peak_src, sm_max_mhz = measured_peaks()
         px = W * H
         bpp = algorithmic_bytes_per_px(n)
         k1_ms, k1_n = kt["search"]          # stage K1 = k1_search + k1_fuse (one launch each per key frame)
@@ -398,49 +475,144 @@ def run_b200(args):
         achieved = bpp["search"] * px / k1_avg_s / 1e9 if k1_avg_s > 0 else 0.0
         alone_us = {k: (v[0] / max(v[1], 1)) * 1e3 for k, v in kt_alone.items()}
         k1_alone_s = (alone_us["search"] + alone_us["fuse"]) * 1e-6
-        traffic = None
+        prof = {}
         try:
             with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
-                traffic = json.load(f).get("dram_bytes_per_launch")
+                prof = json.load(f)
         except Exception:
             pass
+        value = rate["value"]
+        sm_mhz = (clocks or {}).get("sm_mhz") or sm_max_mhz
+        issue = None
+        if prof.get("warp_instructions_per_keyframe"):
+            # the bound that binds: warp instructions the path issues per key frame against the machine's
+            # issue slots (148 SMs x 4 schedulers x SM clock) over the time a key frame takes in the timed region
+            wi = float(prof["warp_instructions_per_keyframe"])
+            slots = 148 * 4 * sm_mhz * 1e6 * (1.0 / (value / world))
+            issue = {"bound": "issue", "warp_instructions_per_keyframe": wi, "issue_slots_per_keyframe": slots,
+                     "frac": wi / slots, "sm_mhz": sm_mhz, "source": prof.get("warp_instructions_source")}
+
+        def e2e_entry(leg):
+            h2d, d2h = bytes_ps[leg]
+            return {"value": rate[leg], "unit": UNIT, "ms_per_step": ms[leg] / args.steps, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": d2h, "host_issue_ms_per_step": host_issue_ms[leg]}
+
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_v / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms["value"] / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args, world), "camera": args.camera, "width": W, "height": H,
-                       "neighbours": n, "keyframes_per_gpu": args.nkf, "l2": "inputs_larger_than_l2",
-                       "parallelism": f"keyframe-shard x{world}" if world > 1 else "single GPU",
-                       "e2e_result": "inverse-depth + sigma maps to pinned host memory; point sets stay device-resident"},
+            "config": config_block(args, world, W, H),
+            "e2e_result": "compact records {pixel, inverse depth, sigma} of every pixel that carries a depth or a sigma (both "
+                          "reference maps, PM.cc:225-226; the consumer expands them) to pinned host memory; e2e_points adds "
+                          "the world point of every record (PM.cc:361-363); e2e_dense = the two maps as dense planes",
             "pixels_per_s": value * px,
-            "e2e": {"value": e2e, "unit": UNIT, "ms_per_step": ms_e / args.steps,
-                    "h2d_bytes_per_step": len(resident) * img_bytes, "d2h_bytes_per_step": len(owned) * 2 * px * 4},
-            "gpu_launches": int(launches),
-            "host_issue_ms_per_step": {"value": host_issue_ms[0] / args.steps, "e2e": host_issue_ms[1] / args.steps},
+            "e2e": e2e_entry("e2e"), "e2e_points": e2e_entry("e2e_points"), "e2e_dense": e2e_entry("e2e_dense"),
+            "gpu_launches": int(launches["value"]),
+            "launches_per_keyframe": launches["value"] / (args.steps * len(wl.owned)),
+            "host_issue_ms_per_step": host_issue_ms,
             "clocks": clocks,
             "roofline": {"kernel": "k1_search + k1_fuse (epipolar search + hypothesis fusion)", "bound": "hbm", "achieved": achieved,
                          "peak": peak, "peak_source": peak_src, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "algorithmic_bytes_per_launch": bpp["search"] * px,
+                         "traffic": prof.get("dram_bytes_per_launch"), "traffic_source": prof.get("source"),
+                         "traffic_measured_at_commit": prof.get("commit"),
+                         "algorithmic_bytes_per_launch": bpp["search"] * px,
                          "avg_launch_us": k1_avg_s * 1e6,
                          "standalone_launch_us": k1_alone_s * 1e6,
                          "standalone_achieved": bpp["search"] * px / k1_alone_s / 1e9 if k1_alone_s > 0 else 0.0,
-                         "whole_path_frac": sum(bpp.values()) * px * (value / world) / 1e9 / peak},
+                         "whole_path_frac": sum(bpp.values()) * px * (value / world) / 1e9 / peak,
+                         "issue": issue},
             "kernels_avg_us": {k: (v[0] / max(v[1], 1)) * 1e3 for k, v in kt.items()},
             "kernels_standalone_us": alone_us,
             "kernels_standalone_share": {k: v / max(sum(alone_us.values()), 1e-9) for k, v in alone_us.items()},
             "valid_fraction": valid_fraction,
         }
-        if world == 1 and not args.no_cpu_baseline:
-            from oracle import pm_oracle as po
-            sample = max(args.cpu_sample, n + 1)
-            dt, _, _, threads = cpu_pass(po, synth, pipeline, args, sample)
-            line["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": f"first {sample} key frames of the same workload, all stages K0..K5, oracle port with OpenMP on the reference's five pragma loops (one pass, {dt:.1f} s)"}
-        emit(line)
+        if seam is not None:
+            line["seam_parity"] = seam
+    wl = None
     ctx.close()
+    if rank == 0 and world == 1 and not args.no_configs:
+        line["configs"] = other_configs(args, torch, pkg, synth, sharding, dev)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        from oracle import pm_oracle as po
+        threads = host_cores()
+        sample = max(args.cpu_sample, n + 1)
+        _, plan, images = cpu_sample_plan(args, synth, po, sample)
+        dt = cpu_pass(po, plan, images, threads)
+        line["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {sample} key frames of the same workload, all stages K0..K5, oracle port with OpenMP on the reference's five pragma loops (one pass, {dt:.1f} s)"}
+    if rank == 0:
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank):
+    """Every rank: the owned key frames with neighbours on another rank -- the first and last N/2 of its range -- against the
+    CPU oracle run on the window around the seam, DEPTH / SIGMA / DEPTH_CHECKED bitwise (the loop being sharded is
+    PM.cc:262-307, the reads across the seam PM.cc:705-752).  Returns the all-reduced counts."""
+    from oracle import pm_oracle as po
+    ctx, n, total = wl.ctx, wl.n, wl.total_kf
+    own = set(wl.owned)
+    seam = [k for k in wl.owned if any(int(j) not in own for j in wl.plan.nbrs[k])]
+    plan = HostPlan(synth, wl.scene, total, n, [], po.stereo_search_constraints, args.prior_sigmas)
+    need_sd = set(seam)
+    for k in seam:
+        need_sd.update(int(j) for j in wl.plan.nbrs[k])
+    for k in sorted(need_sd):
+        plan.add(synth, total, n, k, po.stereo_search_constraints, args.prior_sigmas)
+    need_img = set(need_sd)
+    for k in need_sd:
+        need_img.update(int(j) for j in plan.nbrs[k])
+    hnp = wl.host_img.numpy()
+    images = {k: (hnp[wl.slot[k]] if k in wl.slot else wl.scene.render(k)) for k in sorted(need_img)}
+    ora = po.Oracle(threads=max(1, host_cores() // world))
+    for k in sorted(need_img):
+        ora.add_keyframe(k, images[k], wl.scene.K, wl.scene.pose(k))
+    for k in sorted(need_sd):
+        ora.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
+    bad = 0
+    for k in seam:
+        ora.interkf(k, plan.nbrs[k])
+        for which in (po.DEPTH, po.SIGMA, po.DEPTH_CHECKED):
+            if not np.array_equal(ctx.plane(k, which), ora.plane(k, which)):
+                bad += 1
+                sys.stderr.write(f"rank {rank}: seam key frame {k} plane {which} differs from the oracle\n")
+    ora.close()
+    t = torch.tensor([len(seam), bad], dtype=torch.int64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return {"keyframes_checked": int(t[0].item()), "planes": 3, "mismatching": int(t[1].item()),
+            "checker": "CPU oracle on the +-N window around every seam, bitwise", "ranks": world}
+
+
+def other_configs(args, torch, pkg, synth, sharding, dev):
+    """Short runs (2 steps) of the other BASELINE.json configurations on one GPU, so that their numbers are the driver's:
+    configs[0] (10 x 640x480, N=6), configs[2] shape (720p, N=20), configs[4] shapes (1080p, N=5 and N=40, prior widened
+    to mean +- 4 sigma)."""
+    peak, _, _ = measured_peaks()
+    out = {}
+    for name, cam, nkf, n, sig in (("config1_480p_n6", "480p", 10, 6, 2.0), ("config3_720p_n20", "720p", 48, 20, 2.0),
+                                   ("config5_1080p_n5", "1080p", 40, 5, 4.0), ("config5_1080p_n40", "1080p", 48, 40, 4.0)):
+        c = pkg.Context(dev.index or 0)
+        w = Workload(torch, pkg, synth, sharding, c, dev, cam, nkf, n, 1, 0, args.seed, sig, legs=("value", "e2e"), record_fill=0.6)
+        res = {}
+        for leg in ("value", "e2e"):
+            for _ in range(2):
+                w.step(leg)
+                c.sync()
+            c.span_begin()
+            steps = 2 if nkf >= 40 else 20
+            for _ in range(steps):
+                w.step(leg)
+            res[leg] = nkf * steps / (c.span_end() * 1e-3)
+        bpp = sum(algorithmic_bytes_per_px(n).values())
+        out[name] = {"camera": cam, "keyframes": nkf, "neighbours": n, "prior_sigmas": sig, "steps": steps,
+                     "value": res["value"], "e2e": res["e2e"], "unit": UNIT, "pixels_per_s": res["value"] * w.W * w.H,
+                     "whole_path_frac": bpp * w.W * w.H * res["value"] / 1e9 / peak,
+                     "d2h_bytes_per_step": w.bytes_per_step("e2e")[1]}
+        w = None
+        c.close()
+    return out
 
 
 _JSON_FD = None

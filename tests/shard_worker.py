@@ -1,10 +1,12 @@
 """One rank of the key-frame-sharded path, used by tests/test_gpu_sharded.py and by
 tools/gpu_shard_nccl.sh.  Launched once per rank with RANK / WORLD_SIZE / MASTER_ADDR / MASTER_PORT set.
 
-  SHARD_BACKEND=nccl : one GPU per rank, the (inverse depth, sigma) halo maps travel GPU->GPU over NCCL
+  SHARD_BACKEND=nccl : one GPU per rank; the (inverse depth, sigma) halo maps travel GPU->GPU through the C ABI's own
+                       exchange (sd_comm_init + sd_halo_exchange: grouped ncclSend / ncclRecv straight out of / into
+                       the key-frame planes); torch.distributed (gloo) only distributes the ncclUniqueId
   SHARD_BACKEND=gloo : every rank on cuda:0 (a single-GPU box), the same maps are staged through host
-                       memory and travel over gloo -- same sharding plan, same sd_export_maps /
-                       sd_import_maps calls, same kernels
+                       memory and travel over gloo -- same sharding plan, sd_export_maps / sd_import_maps,
+                       same kernels
 
 Every rank checks the key frames it owns against the CPU oracle run on the WHOLE sequence: sharding
 must not change a single value.  Exit code 0 = parity."""
@@ -35,7 +37,7 @@ def main():
     local = rank if backend == "nccl" else 0
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    dist.init_process_group(backend, rank=rank, world_size=world)
+    dist.init_process_group("gloo", rank=rank, world_size=world)   # plumbing only: unique id, staged maps, barrier
 
     small = dict(w=320, h=240, fx=262.5, fy=262.5, cx=159.5, cy=119.5)
     scene = synth.Scene(small if cam == "small" else cam, seed=77)
@@ -48,6 +50,12 @@ def main():
     for k in shard.resident:                              # owned + image halo: K0 is recomputed locally
         ctx.upload_keyframe(k, images[k], scene.K, plan.poses[k])
     ext = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
+    halo = None
+    if backend == "nccl":
+        ids = [pkg.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0)
+        ctx.comm_init(world, rank, ids[0])
+        halo = ctx.make_halo(shard.send, shard.recv)
 
     def pack(ids):
         t = torch.empty((len(ids), 2, H, W), dtype=torch.float32, device=dev)
@@ -55,10 +63,10 @@ def main():
             for i, k in enumerate(ids):
                 ctx.export_maps(k, t[i, 0].data_ptr(), t[i, 1].data_ptr())
         ctx.sync()
-        return t if backend == "nccl" else t.cpu()
+        return t.cpu()
 
     def alloc(cnt):
-        return torch.empty((cnt, 2, H, W), dtype=torch.float32, device=dev if backend == "nccl" else "cpu")
+        return torch.empty((cnt, 2, H, W), dtype=torch.float32, device="cpu")
 
     keep = []
 
@@ -76,11 +84,14 @@ def main():
             k = op[1]
             ctx.semidense(k, plan.nbrs[k], plan.rots[k], *plan.prior[k])
         elif op[0] == "exchange":
-            with torch.cuda.stream(ext):                  # NCCL orders against the context's compute stream
-                nbytes = sharding.exchange_maps(shard, dist, pack, alloc, unpack)
+            if backend == "nccl":
+                ctx.halo_exchange(halo)                   # on the context's compute stream, no staging
+                nbytes = 2 * 4 * W * H * (sum(map(len, shard.send.values())) + sum(map(len, shard.recv.values())))
+            else:
+                with torch.cuda.stream(ext):
+                    nbytes = sharding.exchange_maps(shard, dist, pack, alloc, unpack)
         else:
-            ctx.interkf_check(op[1], plan.nbrs[op[1]])
-            ctx.update_pointset(op[1])
+            ctx.interkf_check_points(op[1], plan.nbrs[op[1]])
     ctx.sync()
 
     ora = po.Oracle(threads=max(1, po.lib().ora_max_threads() // world))

@@ -24,7 +24,7 @@ def _check_common(d):
 
 
 def test_committed_gpu_line_has_the_contract_keys():
-    paths = sorted(glob.glob(os.path.join(ROOT, "profiles", "r01*_bench.json")))
+    paths = sorted(glob.glob(os.path.join(ROOT, "profiles", "r0*_bench.json")))
     assert paths, "no committed bench line under profiles/"
     with open(paths[-1]) as f:
         d = json.loads(f.readline())
@@ -56,3 +56,19 @@ def test_reference_arm_prints_one_conforming_line(built):
     assert d["impl"] == "reference"
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0 and d["e2e"]["value"] == d["value"]
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] == d["value"]
+    # the arm sizes the oracle from the CPUs it may run on, not from OMP_NUM_THREADS (torchrun exports 1), and never
+    # loads the product library
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert d["cpu_baseline_1thread"]["cores"] == 1 and d["cpu_baseline_1thread"]["value"] > 0
+    for k in ("camera", "width", "height", "neighbours", "keyframes_per_gpu", "parallelism", "l2"):
+        assert k in d["config"], k
+
+
+def test_reference_arm_ignores_omp_num_threads_and_product_library(built):
+    env = dict(os.environ, OMP_NUM_THREADS="1", LD_DEBUG="files")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--steps", "1", "--warmup", "1",
+                        "--camera", "480p", "--nbr", "6", "--cpu-sample", "7"], capture_output=True, text=True, timeout=900, env=env)
+    assert r.returncode == 0, r.stderr[-2000:]
+    d = json.loads([ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")][-1])
+    assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
+    assert "libpm_oracle.so" in r.stderr and "libsdpm.so" not in r.stderr

@@ -1,6 +1,6 @@
 """SURVEY.md section 8(e) on a GPU: the key-frame-sharded path with its one exchange step, two ranks.  On the
 single-GPU test box both ranks share cuda:0 and the halo maps are staged over gloo; with >= 2 GPUs the
-same worker runs one rank per GPU over NCCL.  Each rank compares the key frames it owns with the
+same worker runs one rank per GPU and the maps travel through the C ABI's NCCL exchange (sd_halo_exchange).  Each rank compares the key frames it owns with the
 oracle run on the whole sequence (bit-exact)."""
 import os
 import socket
