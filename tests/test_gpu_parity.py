@@ -349,7 +349,7 @@ def test_error_codes(pkg, synth, pipeline):
     with pytest.raises(pkg.SdError) as e:
         ctx.release_keyframe(1)
     assert e.value.code == -2
-    assert ctx.launch_count() >= 4
+    assert ctx.launch_count() >= 2
     ctx.close()
 
 
