@@ -33,6 +33,7 @@ struct Slot {
     uint8_t* gray = nullptr;
     float *grad = nullptr, *theta = nullptr, *depth = nullptr, *sigma = nullptr, *depth_chk = nullptr;
     uint32_t* arc = nullptr;  // SD_ARC_PLANES orientation-arc bit planes (k0_gradient)
+    uint4* rec = nullptr;     // search records: one 16-byte {theta, grad, grad below, im | im below << 16} per pixel (k0_gradient)
     float* points = nullptr;
     uint32_t* list = nullptr;   // active pixels (k0_gradient), input of k1_search
     uint32_t* vlist = nullptr;  // pixels carrying a depth after the intra-KF stage (k23_intra), input of k4_inter_check
@@ -155,7 +156,8 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     const size_t uplane = align_up((size_t)c->pitch_u8 * c->H, 256);
     const size_t lplane = align_up((size_t)c->W * c->H * sizeof(uint32_t), 256);
     const size_t aplane = align_up((size_t)SD_ARC_PLANES * c->H * c->arc_pitch * sizeof(uint32_t), 256);
-    const size_t total = uplane + 5 * fplane + aplane + 2 * lplane + 256;
+    const size_t rplane = align_up((size_t)c->pitch_f * c->H * sizeof(uint4), 256);
+    const size_t total = uplane + 5 * fplane + aplane + rplane + 2 * lplane + 256;
     cudaError_t e = cudaMalloc(&s->slab, total);
     if (e != cudaSuccess) {
         delete s;
@@ -166,6 +168,7 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->grad = (float*)p; p += fplane;
     s->theta = (float*)p; p += fplane;
     s->arc = (uint32_t*)p; p += aplane;
+    s->rec = (uint4*)p; p += rplane;
     s->depth = (float*)p; p += fplane;
     s->sigma = (float*)p; p += fplane;
     s->depth_chk = (float*)p; p += fplane;
@@ -304,7 +307,7 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         ScopedTimer t(c, c->s_up, T_GRAD);
         dim3 blk(K0_TX, K0_TY), grd((w + K0_TW - 1) / K0_TW, (h + K0_TY - 1) / K0_TY);
         k0_gradient<<<grd, blk, 0, c->s_up>>>(s->gray, c->pitch_u8, w, h, s->grad, s->theta, c->pitch_f, s->arc, c->arc_pitch,
-                                              s->list, s->meta, c->P.lambdaG, c->P.lambdaTheta, c->P.border);
+                                              s->rec, s->list, s->meta, c->P.lambdaG, c->P.lambdaTheta, c->P.border);
     }
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_up, c->s_up));
@@ -360,7 +363,7 @@ void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
     A.chi_fuse = c->chi_fuse_f;
     A.THETA = c->P.theta;
     A.inv_THETA = 1 / c->P.theta;
-    A.img = s->gray; A.grad = s->grad; A.theta = s->theta;
+    A.img = s->gray; A.grad = s->grad; A.theta = s->theta; A.rec = s->rec;
     A.list = s->list; A.meta = s->meta;
     A.count_override = -1;
     A.task_counter = &s->meta->k1_task;
@@ -375,7 +378,7 @@ void fill_nbr(Slot* s, Slot* nb, float rot, NbrConst& N) {
     for (int k = 0; k < 3; ++k) { N.Rd0[k] = (double)N.R[k]; N.Rd2[k] = (double)N.R[6 + k]; }
     N.td0 = (double)N.t[0];
     N.td2 = (double)N.t[2];
-    N.img = nb->gray; N.grad = nb->grad; N.theta = nb->theta; N.arc = nb->arc; N.meta = nb->meta;
+    N.img = nb->gray; N.grad = nb->grad; N.theta = nb->theta; N.arc = nb->arc; N.rec = nb->rec; N.meta = nb->meta;
 }
 
 }  // namespace

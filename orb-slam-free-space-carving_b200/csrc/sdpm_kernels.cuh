@@ -47,6 +47,7 @@ struct NbrConst {  // per neighbour, warp-uniform, lives in kernel parameter (co
     const float* grad;
     const float* theta;
     const uint32_t* arc;  // SD_ARC_PLANES bit planes, see k0_gradient
+    const uint4* rec;     // search records, see k0_gradient
     const KfMeta* meta;
 };
 
@@ -63,6 +64,7 @@ struct SearchArgs {
     const uint8_t* img;
     const float* grad;
     const float* theta;
+    const uint4* rec;    // search records of the key frame itself (own-pixel intensity, gradient, orientation in one load)
     const uint32_t* list;
     const KfMeta* meta;
     int count_override;  // >= 0: use instead of meta->active_count (probes)
@@ -170,12 +172,21 @@ constexpr int SD_ARC_PLANES = SD_ARC_CELLS + 1;
 #define SD_ARC_CELL_DEG 11.25f
 #define SD_ARC_MARGIN 0.05f
 
+__device__ __forceinline__ float sobel_mag(int p00, int p01, int p02, int p10, int p12, int p20, int p21, int p22, float& gx, float& gy) {
+    const int sx = (p02 + 2 * p12 + p22) - (p00 + 2 * p10 + p20);
+    const int sy = (p20 + 2 * p21 + p22) - (p00 + 2 * p01 + p02);
+    gx = (float)sx * 0.125f;
+    gy = (float)sy * 0.125f;
+    return sqrtf(gx * gx + gy * gy);
+}
+
 __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __restrict__ img, int pitch_u8, int W, int H,
                                                             float* __restrict__ grad, float* __restrict__ theta, int pitch_f,
-                                                            uint32_t* __restrict__ arc, int arc_pitch,
+                                                            uint32_t* __restrict__ arc, int arc_pitch, uint4* __restrict__ rec,
                                                             uint32_t* __restrict__ list, KfMeta* __restrict__ meta,
                                                             float lambdaG, float lambdaTheta, int border) {
-    __shared__ uint8_t tile[K0_TY + 2][K0_TW + 8];  // column c <-> x0 - 1 + c
+    __shared__ uint8_t tile[K0_TY + 3][K0_TW + 8];  // column c <-> x0 - 1 + c; row r <-> clamp(y0 - 1 + r)
+    __shared__ float s_g[K0_TY + 1][K0_TW];          // GradImg of the tile rows and of the row below the tile (records)
     __shared__ uint32_t s_memb[K0_TY][K0_TW];        // per pixel: bit s = member of arc plane s
     __shared__ int warp_cnt[K0_TY];
     __shared__ int block_base;
@@ -188,7 +199,7 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
     if (x0 + K0_TW < W) {
         // interior columns: the 128 tile bytes of a row are 32 aligned words (x0 and the pitch are multiples of 128),
         // plus one halo byte on each side; rows clamp to the image (replicate border)
-        for (int i = tid; i < (K0_TY + 2) * 34; i += K0_TX * K0_TY) {
+        for (int i = tid; i < (K0_TY + 3) * 34; i += K0_TX * K0_TY) {
             const int r = i / 34, k = i - r * 34;
             const uint8_t* row = img + (size_t)clampi(y0 - 1 + r, 0, H - 1) * pitch_u8;
             if (k < 32) {
@@ -202,7 +213,7 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
             }
         }
     } else {
-        for (int i = tid; i < (K0_TY + 2) * (K0_TW + 2); i += K0_TX * K0_TY) {
+        for (int i = tid; i < (K0_TY + 3) * (K0_TW + 2); i += K0_TX * K0_TY) {
             int r = i / (K0_TW + 2), c = i - r * (K0_TW + 2);
             int yy = clampi(y0 - 1 + r, 0, H - 1), xx = clampi(x0 - 1 + c, 0, W - 1);
             tile[r][c] = __ldg(img + (size_t)yy * pitch_u8 + xx);
@@ -214,6 +225,7 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
     const int xb = x0 + tx * K0_PX;
     const float arcR = lambdaTheta + 0.5f * SD_ARC_CELL_DEG + SD_ARC_MARGIN;
     float g[K0_PX], th[K0_PX];
+    uint32_t pk[K0_PX];
     unsigned long long s1 = 0, s2 = 0;
     uint32_t act[K0_PX];
     int nact = 0;
@@ -223,10 +235,10 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
         int p00 = tile[r - 1][c - 1], p01 = tile[r - 1][c], p02 = tile[r - 1][c + 1];
         int p10 = tile[r][c - 1], p11 = tile[r][c], p12 = tile[r][c + 1];
         int p20 = tile[r + 1][c - 1], p21 = tile[r + 1][c], p22 = tile[r + 1][c + 1];
-        int sx = (p02 + 2 * p12 + p22) - (p00 + 2 * p10 + p20);
-        int sy = (p20 + 2 * p21 + p22) - (p00 + 2 * p01 + p02);
-        float gx = (float)sx * 0.125f, gy = (float)sy * 0.125f;
-        g[i] = sqrtf(gx * gx + gy * gy);
+        float gx, gy;
+        g[i] = sobel_mag(p00, p01, p02, p10, p12, p20, p21, p22, gx, gy);
+        s_g[ty][c - 1] = g[i];
+        pk[i] = (uint32_t)p11 | ((uint32_t)p21 << 16);  // tile rows are clamped at load: p21 is row min(y + 1, H - 1)
         th[i] = fast_atan2_deg(gy, gx);
         const int x = xb + i;
         const bool on = (g[i] >= lambdaG) && x < W && y < H;
@@ -247,6 +259,14 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
             if (on && x >= border && x < W - border && y >= border && y < H - border) act[nact++] = ((uint32_t)y << 16) | (uint32_t)x;
         }
     }
+    // GradImg of the row below the tile (image row y0 + K0_TY), for the records of the tile's last row
+    if (tid < K0_TW && y0 + K0_TY < H) {
+        const int c = tid + 1, r = K0_TY + 1;
+        float gx, gy;
+        s_g[K0_TY][tid] = sobel_mag(tile[r - 1][c - 1], tile[r - 1][c], tile[r - 1][c + 1], tile[r][c - 1], tile[r][c + 1],
+                                    tile[r + 1][c - 1], tile[r + 1][c], tile[r + 1][c + 1], gx, gy);
+    }
+    __syncthreads();
     if (y < H) {
         const size_t o = (size_t)y * pitch_f + xb;
         if (xb + K0_PX <= W) {  // pitch_f and xb are multiples of 4: aligned float4 stores
@@ -256,6 +276,12 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __
             for (int i = 0; i < K0_PX; ++i)
                 if (xb + i < W) { grad[o + i] = g[i]; theta[o + i] = th[i]; }
         }
+#pragma unroll
+        for (int i = 0; i < K0_PX; ++i)
+            if (xb + i < W) {
+                const float gn = (y + 1 < H) ? s_g[ty + 1][tx * K0_PX + i] : g[i];  // second bilinear row clamps to the image
+                rec[o + i] = make_uint4(__float_as_uint(th[i]), __float_as_uint(g[i]), __float_as_uint(gn), pk[i]);
+            }
     }
 
     // 128 pixels x 32 planes -> 32 planes x 4 words: the warp (one image row of the tile) transposes four 32x32 bit
@@ -351,6 +377,28 @@ __device__ __forceinline__ float bilinear_col(const T* __restrict__ pl, int pitc
     return v0 * w0 + v1 * w1;
 }
 
+// (float)u for 0 <= u < 2^23 without the conversion pipe: 2^23 + u is exact, so is the subtraction
+__device__ __forceinline__ float small_int_to_float(int u) { return __int_as_float(0x4B000000 | u) - 8388608.0f; }
+
+// bilinear<uchar>(im_, y, x) and bilinear<float>(GradImg, y, x) of PM.cc:40-59 at an integer column, both from ONE search
+// record (k0_gradient): same arithmetic as bilinear_col.  Row y0 = floor(yv) clamps to the image; the record of the
+// clamped row holds the row below it (itself clamped), and for y0 < 0 both taps are row 0.
+__device__ __forceinline__ void bilinear_rec(const uint4* __restrict__ rec, int pitch, int W, int H, float yv, int uj, float& vI, float& vG) {
+    const float fl = floorf(yv);
+    const int y0 = (int)fl;
+    const float w0 = (float)(y0 + 1) - yv;  // y0_weight = y1 - y
+    const float w1 = 1.0f - w0;             // y1_weight
+    const int xc = clampi(uj, 0, W - 1);
+    const uint4 r = __ldg(rec + (unsigned)(clampi(y0, 0, H - 1) * pitch + xc));
+    const bool above = y0 < 0;
+    const float i0 = small_int_to_float((int)(r.w & 0xffffu));
+    const float i1 = above ? i0 : small_int_to_float((int)(r.w >> 16));
+    const float g0 = __uint_as_float(r.y);
+    const float g1 = above ? g0 : __uint_as_float(r.z);
+    vI = i0 * w0 + i1 * w1;
+    vG = g0 * w0 + g1 * w1;
+}
+
 // GetPixelDepth, PM.cc:845-875 (Eq. 8).  d2 = R21.row(2)*xp, d0 = R21.row(0)*xp accumulated in double
 // (cv::gemm general path); num1 = (float)(d2*ucx), num2f = (float)(d0*fx) is hoisted by the caller.
 __device__ __forceinline__ float pixel_inv_depth(float u, float cx, double d2, float num2f, float t2, float den2) {
@@ -380,9 +428,6 @@ __device__ __forceinline__ bool orientation_gates(float T2, float th_epi, float 
     if (e > 180) e = 360 - e;
     return !(d > lambdaL) && !(e > lambdaTheta);
 }
-
-// (float)u for 0 <= u < 2^23 without the conversion pipe: 2^23 + u is exact, so is the subtraction
-__device__ __forceinline__ float small_int_to_float(int u) { return __int_as_float(0x4B000000 | u) - 8388608.0f; }
 
 // Image row of candidate column u on the epipolar line.  The reference computes
 // vj = -(int)((a/b)*uj + c/b) (PM.cc:407) and rejects vj <= 0 || vj >= rows (PM.cc:408).  With
@@ -590,9 +635,13 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         y = (int)(e >> 16);
     }
     const float xf = (float)x, yf = (float)y;
-    const float I1 = valid ? (float)__ldg(A.img + (size_t)y * A.pitch_u8 + x) : 0.f;  // PM.cc:202
-    const float g1 = valid ? __ldg(A.grad + (size_t)y * A.pitch_f + x) : 0.f;         // PM.cc:434
-    const float th1 = valid ? __ldg(A.theta + (size_t)y * A.pitch_f + x) : 0.f;       // PM.cc:214
+    float I1 = 0.f, g1 = 0.f, th1 = 0.f;
+    if (valid) {  // the pixel's own record: intensity (PM.cc:202), GradImg (PM.cc:434), GradTheta (PM.cc:214)
+        const uint4 own = __ldg(A.rec + (unsigned)(y * A.pitch_f + x));
+        I1 = small_int_to_float((int)(own.w & 0xffffu));
+        g1 = __uint_as_float(own.y);
+        th1 = __uint_as_float(own.x);
+    }
     const float xp0 = (xf - A.cx) / A.fx, xp1 = (yf - A.cy) / A.fy;                   // PM.cc:893, 862
 
     {
@@ -674,15 +723,12 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                     float vf;
                     const int r0 = line_row(p4.x, p4.y, small_int_to_float(uq), vf);  // 0 < r0 < H by construction
                     const int xc = min(uq, A.W - 1);
-                    const int dr = (r0 + 1 < A.H) ? 1 : 0;  // second bilinear row clamps to the image (H2)
-                    const unsigned of0 = (unsigned)(r0 * A.pitch_f + xc);  // planes hold < 2^31 elements (checked at upload)
-                    const unsigned ob0 = (unsigned)(r0 * A.pitch_u8 + xc);
-                    // all five taps are requested before the gates are known (3 of 4 queued candidates pass them)
-                    const float T2 = __ldg(N.theta + of0);
-                    const float gg0 = __ldg(N.grad + of0);
-                    const float gg1 = __ldg(N.grad + of0 + (unsigned)(dr * A.pitch_f));
-                    const float i0 = (float)__ldg(N.img + ob0);
-                    const float i1 = (float)__ldg(N.img + ob0 + (unsigned)(dr * A.pitch_u8));
+                    // one record = orientation + both rows of both bilinear taps (second row clamped to the image, H2);
+                    // requested before the gates are known (3 of 4 queued candidates pass them)
+                    const uint4 rc = __ldg(N.rec + (unsigned)(r0 * A.pitch_f + xc));  // planes hold < 2^31 elements (checked at upload)
+                    const float T2 = __uint_as_float(rc.x);
+                    const float gg0 = __uint_as_float(rc.y), gg1 = __uint_as_float(rc.z);
+                    const float i0 = small_int_to_float((int)(rc.w & 0xffffu)), i1 = small_int_to_float((int)(rc.w >> 16));
                     const float cur = __uint_as_float(beste[owner]);
                     if (orientation_gates(T2, p2.x, p2.y, A.lambdaL, A.lambdaTheta)) {
                         const float yv = -vf;
@@ -815,14 +861,16 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         const bool found = bj >= 0;
         if (found) {
             const float yb = -(abD * (float)bj + cbD);
-            const float rI = I1D - bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yb, bj);
-            const float rG = g1D - bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yb, bj);
+            float bI, bG, pI, pG, mI, mG;
+            bilinear_rec(N.rec, A.pitch_f, A.W, A.H, yb, bj, bI, bG);
+            const float rI = I1D - bI;
+            const float rG = g1D - bG;
             const int up = bj + 1, um = bj - 1;
             const float yp = -(abD * (float)up + cbD), ym = -(abD * (float)um + cbD);
-            const float g = (bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, yp, up) -
-                             bilinear_col<uint8_t>(N.img, A.pitch_u8, A.W, A.H, ym, um)) / 2;
-            const float q = (bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, yp, up) -
-                             bilinear_col<float>(N.grad, A.pitch_f, A.W, A.H, ym, um)) / 2;
+            bilinear_rec(N.rec, A.pitch_f, A.W, A.H, yp, up, pI, pG);
+            bilinear_rec(N.rec, A.pitch_f, A.W, A.H, ym, um, mI, mG);
+            const float g = (pI - mI) / 2;
+            const float q = (pG - mG) / 2;
             const double itq = A.inv_THETA * (double)q;                           // (1/THETA)*q
             const float den = (float)((double)(g * g) + itq * (double)q);         // PM.cc:455
             const float ustar = (float)((double)bj + ((double)(g * rI) + itq * (double)rG) / (double)den);  // PM.cc:456
