@@ -73,7 +73,9 @@ struct sd_ctx {
     cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
-    float *tmp_depth = nullptr, *tmp_sigma = nullptr;  // k1_fuse output / k23_intra input
+    // k1_fuse output / k23_intra input, one pair per hypothesis buffer; invariant: all zero while no key frame is in
+    // flight on the buffer (k23_intra is followed by the memsets that restore it, off the key frame's own dependency chain)
+    float *tmp_depth[2] = {nullptr, nullptr}, *tmp_sigma[2] = {nullptr, nullptr};
     float2* hyp[2] = {nullptr, nullptr};               // hypothesis buffers of k1_search, [neighbour][hyp_stride], double-buffered
     int hyp_stride = 0, hyp_rows = 0, hyp_turn = 0;
     cudaEvent_t ev_srch[2] = {nullptr, nullptr};       // k1_search into hyp[b] done (s_srch)
@@ -268,8 +270,12 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         c->pitch_u8 = (int)align_up(w, 128);
         c->arc_pitch = 4 * ((w + K0_TW - 1) / K0_TW);  // u32 words per bit-plane row, whole K0 tiles
         const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
-        CU(c, cudaMalloc(&c->tmp_depth, fplane));
-        CU(c, cudaMalloc(&c->tmp_sigma, fplane));
+        for (int b = 0; b < 2; ++b) {
+            CU(c, cudaMalloc(&c->tmp_depth[b], fplane));
+            CU(c, cudaMalloc(&c->tmp_sigma[b], fplane));
+            CU(c, cudaMemset(c->tmp_depth[b], 0, fplane));
+            CU(c, cudaMemset(c->tmp_sigma[b], 0, fplane));
+        }
     } else if (c->W != w || c->H != h) {
         return fail(c, SD_ERR_SHAPE, "key frame %d is %dx%d, context is %dx%d", kf_id, w, h, c->W, c->H);
     }
@@ -470,8 +476,10 @@ int sd_destroy(sd_ctx* c) {
     for (auto* s : c->free_slots) free_slot(s);
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : c->ev_pool) cudaEventDestroy(e);
-    cudaFree(c->tmp_depth);
-    cudaFree(c->tmp_sigma);
+    for (int b = 0; b < 2; ++b) {
+        cudaFree(c->tmp_depth[b]);
+        cudaFree(c->tmp_sigma[b]);
+    }
     cudaFree(c->hyp[0]);
     cudaFree(c->hyp[1]);
     for (int b = 0; b < 2; ++b) {
@@ -563,22 +571,24 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     A.hyp = c->hyp[hb];
     A.hyp_stride = c->hyp_stride;
     // ---- search stream: k1_search of this key frame into hyp[hb] ----
-    CU(c, cudaStreamWaitEvent(c->s_srch, s->ev_up, 0));
+    cudaStream_t s_srch = c->s_srch;
+    CU(c, cudaStreamWaitEvent(s_srch, s->ev_up, 0));
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
         if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
         fill_nbr(s, nb, nbr_rot_deg ? nbr_rot_deg[j] : 0.f, A.nb[j]);
-        CU(c, cudaStreamWaitEvent(c->s_srch, nb->ev_up, 0));
+        CU(c, cudaStreamWaitEvent(s_srch, nb->ev_up, 0));
     }
-    if (c->hypfree_valid[hb]) CU(c, cudaStreamWaitEvent(c->s_srch, c->ev_hypfree[hb], 0));
-    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), c->s_srch));
+    // buffers [hb] are free once the k23_intra of their previous key frame has read them and they are zero again
+    if (c->hypfree_valid[hb]) CU(c, cudaStreamWaitEvent(s_srch, c->ev_hypfree[hb], 0));
+    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), s_srch));
     {
         const int grid = c->k1_grid;
-        ScopedTimer t(c, c->s_srch, T_SEARCH);
-        k1_search<<<grid, K1_WARPS * 32, 0, c->s_srch>>>(A);
+        ScopedTimer t(c, s_srch, T_SEARCH);
+        k1_search<<<grid, K1_WARPS * 32, 0, s_srch>>>(A);
     }
-    CU(c, cudaEventRecord(c->ev_srch[hb], c->s_srch));
-    // ---- main stream: fusion into the scratch planes (zero = no depth), then k23_intra reads them with a
+    CU(c, cudaEventRecord(c->ev_srch[hb], s_srch));
+    // ---- main stream: fusion into the scratch planes [hb] (zero = no depth), then k23_intra reads them with a
     // halo and writes the key frame's own planes ----
     CU(c, cudaStreamWaitEvent(c->s_main, c->ev_srch[hb], 0));
     if (s->dn_pending) {  // a download of the old maps may still be in flight
@@ -587,14 +597,12 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     }
     CU(c, wait_map_readers(c, s, c->s_main));  // k23_intra below overwrites this key frame's maps and list
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
-    CU(c, cudaMemsetAsync(c->tmp_depth, 0, fplane, c->s_main));
-    CU(c, cudaMemsetAsync(c->tmp_sigma, 0, fplane, c->s_main));
     CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_main));
     {
         ScopedTimer t(c, c->s_main, T_FUSE);
         FuseArgs F;
         F.n = n; F.lambdaN = c->P.lambdaN; F.pitch_f = c->pitch_f; F.hyp_stride = c->hyp_stride; F.chi_fuse = c->chi_fuse_f;
-        F.hyp = c->hyp[hb]; F.list = s->list; F.meta = s->meta; F.depth = c->tmp_depth; F.sigma = c->tmp_sigma;
+        F.hyp = c->hyp[hb]; F.list = s->list; F.meta = s->meta; F.depth = c->tmp_depth[hb]; F.sigma = c->tmp_sigma[hb];
         const int blocks = ((c->W - 2 * c->P.border) * (c->H - 2 * c->P.border) + 127) / 128;  // the list's capacity
         if (n <= 6) k1_fuse<6><<<blocks, 128, 0, c->s_main>>>(F);
         else if (n <= 10) k1_fuse<10><<<blocks, 128, 0, c->s_main>>>(F);
@@ -604,19 +612,22 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
             k1_fuse_rows<<<(cap + K1FR_THREADS - 1) / K1FR_THREADS, K1FR_THREADS, k1fr_smem_bytes(n), c->s_main>>>(F);
         }
     }
-    CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
-    c->hypfree_valid[hb] = true;
     {
         ScopedTimer t(c, c->s_main, T_INTRA);
         IntraArgs S;
         S.W = c->W; S.H = c->H; S.pitch_in = c->pitch_f; S.pitch_out = c->pitch_f; S.border = c->P.border; S.vec_ok = 1;
         S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f;
-        S.depth_in = c->tmp_depth; S.sigma_in = c->tmp_sigma; S.grad = s->grad;
+        S.depth_in = c->tmp_depth[hb]; S.sigma_in = c->tmp_sigma[hb]; S.grad = s->grad;
         S.depth_out = s->depth; S.sigma_out = s->sigma; S.depth_copy = s->depth_chk;
         S.vlist = s->vlist; S.vcount = &s->meta->valid_count;
         dim3 grd((c->W + K23_TW - 1) / K23_TW, (c->H + K23_TH - 1) / K23_TH);
         k23_intra<true, true><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
     }
+    // the scratch planes go back to all-zero for the next key frame that uses buffers [hb]
+    CU(c, cudaMemsetAsync(c->tmp_depth[hb], 0, fplane, c->s_main));
+    CU(c, cudaMemsetAsync(c->tmp_sigma[hb], 0, fplane, c->s_main));
+    CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
+    c->hypfree_valid[hb] = true;
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_sd, c->s_main));
     s->sd_recorded = true;

@@ -180,7 +180,10 @@ __device__ __forceinline__ float sobel_mag(int p00, int p01, int p02, int p10, i
     return sqrtf(gx * gx + gy * gy);
 }
 
-__global__ void __launch_bounds__(K0_TX* K0_TY, 6) k0_gradient(const uint8_t* __restrict__ img, int pitch_u8, int W, int H,
+#ifndef K0_MIN_BLOCKS
+#define K0_MIN_BLOCKS 6
+#endif
+__global__ void __launch_bounds__(K0_TX* K0_TY, K0_MIN_BLOCKS) k0_gradient(const uint8_t* __restrict__ img, int pitch_u8, int W, int H,
                                                             float* __restrict__ grad, float* __restrict__ theta, int pitch_f,
                                                             uint32_t* __restrict__ arc, int arc_pitch, uint4* __restrict__ rec,
                                                             uint32_t* __restrict__ list, KfMeta* __restrict__ meta,
@@ -561,6 +564,7 @@ __device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const flo
 constexpr int K1_WARPS = K1_WARPS_PER_BLOCK;
 constexpr int K1_QHALF = 512;           // what 16 lanes can queue in one scan step (16 lanes x 32 columns)
 constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller step is queued in two halves
+constexpr int K1_WARP_SMEM = 512 + 256 + 4 * K1_QCAP + 4 * 128;  // 3 456 bytes per warp
 #ifndef K1F_MIN_BLOCKS
 #define K1F_MIN_BLOCKS 8
 #endif
@@ -591,24 +595,21 @@ constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller st
 //  (D) per lane: sub-pixel refinement and inverse-depth hypothesis (PM.cc:446-463, 806-829), written
 //      to the hypothesis buffer [neighbour][entry]; k1_fuse turns the buffer into the maps.
 __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const __grid_constant__ SearchArgs A) {
-    __shared__ uint32_t s_queue[K1_WARPS][K1_QCAP];
-    __shared__ float4 s_par4[K1_WARPS][32];  // per owner lane: a/b, c/b, I1, GradImg1
-    __shared__ float2 s_par2[K1_WARPS][32];  // per owner lane: epipolar-line angle, rotated orientation
-    __shared__ uint32_t s_beste[K1_WARPS][32];
-    __shared__ uint32_t s_bestu[K1_WARPS][32];
-    __shared__ uint32_t s_tie[K1_WARPS][32];  // per owner lane: two best errs too close for the float shortcut
-    __shared__ uint32_t s_rng[K1_WARPS][32];  // per lane: u_lo | (u_hi + 1) << 16 -- parked for phase (D), which is register-lean
+    // one region per warp: par4 | par2 | queue | beste | bestu | tie | rng
+    __shared__ __align__(16) unsigned char s_warp[K1_WARPS][K1_WARP_SMEM];
 
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
     const int count = A.count_override >= 0 ? A.count_override : A.meta->active_count;
 
-    uint32_t* queue = s_queue[wib];
-    uint32_t* beste = s_beste[wib];
-    uint32_t* bestu = s_bestu[wib];
-    float4* par4 = s_par4[wib];
-    float2* par2 = s_par2[wib];
-    uint32_t* tie = s_tie[wib];
+    unsigned char* const wsm = s_warp[wib];
+    float4* par4 = reinterpret_cast<float4*>(wsm);                 // per owner lane: a/b, c/b, I1, GradImg1
+    float2* par2 = reinterpret_cast<float2*>(wsm + 512);           // per owner lane: epipolar-line angle, rotated orientation
+    uint32_t* queue = reinterpret_cast<uint32_t*>(wsm + 768);      // K1_QCAP entries
+    uint32_t* beste = queue + K1_QCAP;
+    uint32_t* bestu = beste + 32;
+    uint32_t* tie = bestu + 32;                                    // per owner lane: two best errs too close for the float shortcut
+    uint32_t* s_rng = tie + 32;                                    // per lane: u_lo | (u_hi + 1) << 16 -- parked for phase (D), which is register-lean
     const float colsf = (float)A.W;
     const float inv_theta_f = (float)A.inv_THETA;
     const size_t arc_plane = (size_t)A.H * A.arc_pitch;
@@ -699,7 +700,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
 
         par4[lane] = make_float4(ab, cb, I1, g1);
         par2[lane] = make_float2(th_epi, apr);
-        s_rng[wib][lane] = (uint32_t)(u_lo & 0xffff) | ((uint32_t)(u_hi + 1) << 16);  // 0 <= u_lo <= W, -1 <= u_hi <= W
+        s_rng[lane] = (uint32_t)(u_lo & 0xffff) | ((uint32_t)(u_hi + 1) << 16);  // 0 <= u_lo <= W, -1 <= u_hi <= W
         beste[lane] = 0x7f800000u;  // +inf
         tie[lane] = 0;
         __syncwarp();
@@ -848,7 +849,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         int bj = -1;
         if (tie[lane]) {
             const float2 own2 = par2[lane];
-            const uint32_t rg = s_rng[wib][lane];
+            const uint32_t rg = s_rng[lane];
             LineScan L;
             L.ab = abD; L.cb = cbD; L.I1 = I1D; L.g1 = g1D; L.th_epi = own2.x; L.apr = own2.y;
             L.u_lo = (int)(rg & 0xffffu); L.u_hi = (int)(rg >> 16) - 1;

@@ -16,7 +16,7 @@ while i < len(rows):
 for name, hdr, body in sections:
     if kern not in name: continue
     ci = hdr.index("Instructions Executed"); cs = hdr.index("# Samples")
-    lines = [(int(r[0]), r[1], int(r[ci] or 0), int(r[cs] or 0)) for r in body if r and r[0].isdigit()]
+    lines = [(int(r[0]), r[1], int(r[ci]) if r[ci].isdigit() else 0, int(r[cs]) if r[cs].isdigit() else 0) for r in body if r and r[0].isdigit()]
     tot = sum(l[2] for l in lines); tots = sum(l[3] for l in lines)
     print(f"== {name}: {tot} warp instructions, {tots} samples")
     for ln, src, n, smp in sorted(lines, key=lambda l: -l[2])[:top]:
