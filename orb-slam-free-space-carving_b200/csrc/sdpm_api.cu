@@ -37,6 +37,7 @@ struct Slot {
     float* points = nullptr;
     uint32_t* list = nullptr;   // active pixels (k0_gradient), input of k1_search
     uint32_t* vlist = nullptr;  // pixels carrying a depth after the intra-KF stage (k23_intra), input of k4_inter_check
+    float* ray = nullptr;       // W + H floats: (x - cx) / fx per column, (y - cy) / fy per row (k0_gradient), read by k1_search
     KfMeta* meta = nullptr;
     bool vlist_ok = false;      // vlist / meta->valid_count describe `depth`
     bool vlist_from_import = false;  // the list was rebuilt from imported planes (which may carry values outside the 2-px frame)
@@ -45,8 +46,10 @@ struct Slot {
     cudaEvent_t ev_dn = nullptr;  // last download issued (s_dn)
     bool dn_pending = false;
     cudaEvent_t ev_sd = nullptr;   // (depth, sigma) maps ready: after k23_intra / sd_import_maps (s_main)
-    cudaEvent_t ev_chk = nullptr;  // last K4 / K5 of this key frame (s_chk)
-    bool sd_recorded = false, chk_recorded = false;
+    // Record numbers (see wait_for_*): every stream is in-order, so waiting for record q of a stream covers all its earlier ones
+    long long up_seq = 0;          // number of this key frame's upload on s_up
+    long long sd_seq = 0;          // number of the ev_sd record on s_main; 0 = no maps yet
+    long long chk_idx = -1;        // ring index of the last K4 / K5 / K6 of this key frame (s_chk); -1 = none
     long long rd_idx = -1;         // ring index of the last K4 that read this key frame's maps (own or as a neighbour)
 };
 
@@ -68,8 +71,12 @@ struct sd_ctx {
     // check of key frame j overlaps the fusion / intra stage of a later one
     cudaStream_t s_up = nullptr, s_srch = nullptr, s_main = nullptr, s_chk = nullptr, s_dn = nullptr;
     static const int RING = 64;
-    cudaEvent_t ev_ring[RING] = {nullptr};  // ev_ring[i % RING]: K4 number i done (s_chk)
+    cudaEvent_t ev_ring[RING] = {nullptr};  // ev_ring[i % RING]: record number i of s_chk (one per K4 / K5 / K6)
     long long ring_i = 0;
+    long long up_seq = 0, sd_seq = 0;       // records issued so far on s_up (uploads) and on s_main (ev_sd)
+    // highest record number of the producing stream that the consuming stream has already waited for
+    long long srch_seen_up = 0, main_seen_up = 0, chk_seen_sd = 0, dn_seen_sd = 0, main_seen_chk = -1, dn_seen_chk = -1;
+    bool dirty = false;  // work has been queued on s_srch / s_main / s_chk / s_dn since s_up last waited for those streams
     cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
@@ -159,7 +166,8 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     const size_t lplane = align_up((size_t)c->W * c->H * sizeof(uint32_t), 256);
     const size_t aplane = align_up((size_t)SD_ARC_PLANES * c->H * c->arc_pitch * sizeof(uint32_t), 256);
     const size_t rplane = align_up((size_t)c->pitch_f * c->H * sizeof(uint4), 256);
-    const size_t total = uplane + 5 * fplane + aplane + rplane + 2 * lplane + 256;
+    const size_t yplane = align_up((size_t)(c->W + c->H) * sizeof(float), 256);
+    const size_t total = uplane + 5 * fplane + aplane + rplane + 2 * lplane + yplane + 256;
     cudaError_t e = cudaMalloc(&s->slab, total);
     if (e != cudaSuccess) {
         delete s;
@@ -176,11 +184,11 @@ int alloc_slot(sd_ctx* c, Slot** out) {
     s->depth_chk = (float*)p; p += fplane;
     s->list = (uint32_t*)p; p += lplane;
     s->vlist = (uint32_t*)p; p += lplane;
+    s->ray = (float*)p; p += yplane;
     s->meta = (KfMeta*)p;
     cudaEventCreateWithFlags(&s->ev_up, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_dn, cudaEventDisableTiming);
     cudaEventCreateWithFlags(&s->ev_sd, cudaEventDisableTiming);
-    cudaEventCreateWithFlags(&s->ev_chk, cudaEventDisableTiming);
     *out = s;
     return SD_OK;
 }
@@ -192,7 +200,6 @@ void free_slot(Slot* s) {
     if (s->ev_up) cudaEventDestroy(s->ev_up);
     if (s->ev_dn) cudaEventDestroy(s->ev_dn);
     if (s->ev_sd) cudaEventDestroy(s->ev_sd);
-    if (s->ev_chk) cudaEventDestroy(s->ev_chk);
     delete s;
 }
 
@@ -271,10 +278,9 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         c->arc_pitch = 4 * ((w + K0_TW - 1) / K0_TW);  // u32 words per bit-plane row, whole K0 tiles
         const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
         for (int b = 0; b < 2; ++b) {
-            CU(c, cudaMalloc(&c->tmp_depth[b], fplane));
-            CU(c, cudaMalloc(&c->tmp_sigma[b], fplane));
-            CU(c, cudaMemset(c->tmp_depth[b], 0, fplane));
-            CU(c, cudaMemset(c->tmp_sigma[b], 0, fplane));
+            CU(c, cudaMalloc(&c->tmp_depth[b], 2 * fplane));  // depth | sigma: one memset restores both
+            c->tmp_sigma[b] = c->tmp_depth[b] + (size_t)c->pitch_f * c->H;
+            CU(c, cudaMemset(c->tmp_depth[b], 0, 2 * fplane));
         }
     } else if (c->W != w || c->H != h) {
         return fail(c, SD_ERR_SHAPE, "key frame %d is %dx%d, context is %dx%d", kf_id, w, h, c->W, c->H);
@@ -288,9 +294,11 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         s->id = kf_id;
         c->kfs[kf_id] = s;
     }
-    if (!fresh) {
+    if (!fresh && c->dirty) {
         // the planes are being replaced (same key frame again, or a slot recycled by sd_release_keyframe):
-        // wait for everything already queued that may still read them
+        // wait for everything already queued that may still read them.  Once per batch of uploads: s_up is in-order,
+        // so while nothing new is queued on the other streams (c->dirty) the earlier wait still covers them
+        c->dirty = false;
         CU(c, cudaEventRecord(c->ev_tmp, c->s_main));
         CU(c, cudaStreamWaitEvent(c->s_up, c->ev_tmp, 0));
         CU(c, cudaEventRecord(c->ev_tmp, c->s_srch));
@@ -302,8 +310,9 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
     }
     s->has_semidense = s->has_checked = s->has_points = s->pose_changed = s->vlist_ok = s->vlist_from_import = false;
     s->dn_pending = false;
-    s->sd_recorded = s->chk_recorded = false;
-    s->rd_idx = -1;
+    s->sd_seq = 0;
+    s->chk_idx = s->rd_idx = -1;
+    s->up_seq = ++c->up_seq;
     std::memcpy(s->K, K, sizeof(s->K));
     set_pose_fields(s, Tcw);
 
@@ -313,22 +322,47 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         ScopedTimer t(c, c->s_up, T_GRAD);
         dim3 blk(K0_TX, K0_TY), grd((w + K0_TW - 1) / K0_TW, (h + K0_TY - 1) / K0_TY);
         k0_gradient<<<grd, blk, 0, c->s_up>>>(s->gray, c->pitch_u8, w, h, s->grad, s->theta, c->pitch_f, s->arc, c->arc_pitch,
-                                              s->rec, s->list, s->meta, c->P.lambdaG, c->P.lambdaTheta, c->P.border);
+                                              s->rec, s->list, s->meta, c->P.lambdaG, c->P.lambdaTheta, c->P.border,
+                                              s->ray, s->K[0], s->K[1], s->K[2], s->K[3]);
     }
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_up, c->s_up));
     return SD_OK;
 }
 
-// Before `stream` overwrites the maps of a key frame: wait for the K4 / K5 launches (s_chk) that read them.
-// ev_ring slots are reused by later K4 launches of the same stream, so a recycled event still implies the
-// one it replaced.
-cudaError_t wait_map_readers(sd_ctx* c, Slot* s, cudaStream_t stream) {
-    cudaError_t e = cudaSuccess;
-    if (s->rd_idx >= 0) e = cudaStreamWaitEvent(stream, c->ev_ring[s->rd_idx % sd_ctx::RING], 0);
-    if (e == cudaSuccess && s->chk_recorded) e = cudaStreamWaitEvent(stream, s->ev_chk, 0);
-    return e;
+// Cross-stream waits.  Every stream of the context is in-order and its records are numbered (uploads on s_up: Slot::up_seq;
+// ev_sd records on s_main: Slot::sd_seq; K4 / K5 / K6 on s_chk: ring indices), so a consumer stream that has waited for
+// record q of a producer stream is past every earlier record of it too: one cudaStreamWaitEvent on the LATEST record
+// needed, none when the consumer has already waited for that one or a later one (`seen`).  An event that has been
+// re-recorded since (the key frame uploaded again, a ring slot reused) marks a later point of the same stream, which
+// still implies the one asked for.
+cudaError_t wait_upload(cudaStream_t stream, long long& seen, const Slot* latest) {
+    if (!latest || latest->up_seq <= seen) return cudaSuccess;
+    seen = latest->up_seq;
+    return cudaStreamWaitEvent(stream, latest->ev_up, 0);
 }
+cudaError_t wait_maps(cudaStream_t stream, long long& seen, const Slot* latest) {
+    if (!latest || latest->sd_seq <= seen) return cudaSuccess;  // sd_seq == 0: no maps recorded
+    seen = latest->sd_seq;
+    return cudaStreamWaitEvent(stream, latest->ev_sd, 0);
+}
+cudaError_t wait_ring(sd_ctx* c, cudaStream_t stream, long long& seen, long long idx) {
+    if (idx <= seen) return cudaSuccess;  // idx == -1: none
+    seen = idx;
+    return cudaStreamWaitEvent(stream, c->ev_ring[idx % sd_ctx::RING], 0);
+}
+// record number of the next K4 / K5 / K6 on s_chk (call right after the launch)
+cudaError_t record_chk(sd_ctx* c, Slot* s) {
+    const long long idx = c->ring_i++;
+    s->chk_idx = idx;
+    return cudaEventRecord(c->ev_ring[idx % sd_ctx::RING], c->s_chk);
+}
+// Before s_main overwrites the maps of a key frame: wait for the K4 launches (s_chk) that read them, as the key frame's
+// own or as a neighbour's, and for its own K5 / K6.
+cudaError_t wait_map_readers(sd_ctx* c, Slot* s) {
+    return wait_ring(c, c->s_main, c->main_seen_chk, std::max(s->rd_idx, s->chk_idx));
+}
+void record_maps(sd_ctx* c, Slot* s) { s->sd_seq = ++c->sd_seq; }
 
 
 // ---- compact downloads: pending queue ----
@@ -369,6 +403,8 @@ void fill_search_common(sd_ctx* c, Slot* s, SearchArgs& A) {
     A.chi_fuse = c->chi_fuse_f;
     A.THETA = c->P.theta;
     A.inv_THETA = 1 / c->P.theta;
+    A.inv_theta_f = (float)A.inv_THETA;
+    A.ray = s->ray;
     A.img = s->gray; A.grad = s->grad; A.theta = s->theta; A.rec = s->rec;
     A.list = s->list; A.meta = s->meta;
     A.count_override = -1;
@@ -477,8 +513,7 @@ int sd_destroy(sd_ctx* c) {
     for (auto& sp : c->spans) { cudaEventDestroy(sp.a); cudaEventDestroy(sp.b); }
     for (auto e : c->ev_pool) cudaEventDestroy(e);
     for (int b = 0; b < 2; ++b) {
-        cudaFree(c->tmp_depth[b]);
-        cudaFree(c->tmp_sigma[b]);
+        cudaFree(c->tmp_depth[b]);  // tmp_sigma[b] is the second half of the same allocation
     }
     cudaFree(c->hyp[0]);
     cudaFree(c->hyp[1]);
@@ -572,16 +607,18 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     A.hyp_stride = c->hyp_stride;
     // ---- search stream: k1_search of this key frame into hyp[hb] ----
     cudaStream_t s_srch = c->s_srch;
-    CU(c, cudaStreamWaitEvent(s_srch, s->ev_up, 0));
+    c->dirty = true;
+    const Slot* latest_up = s;  // the search reads the planes of kf and of its neighbours: wait for the last of those uploads
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
         if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
         fill_nbr(s, nb, nbr_rot_deg ? nbr_rot_deg[j] : 0.f, A.nb[j]);
-        CU(c, cudaStreamWaitEvent(s_srch, nb->ev_up, 0));
+        if (nb->up_seq > latest_up->up_seq) latest_up = nb;
     }
+    CU(c, wait_upload(s_srch, c->srch_seen_up, latest_up));
     // buffers [hb] are free once the k23_intra of their previous key frame has read them and they are zero again
     if (c->hypfree_valid[hb]) CU(c, cudaStreamWaitEvent(s_srch, c->ev_hypfree[hb], 0));
-    CU(c, cudaMemsetAsync(&s->meta->k1_task, 0, sizeof(unsigned int), s_srch));
+    // meta->k1_task is zero here: zeroed with the meta block at upload, and again by the last warp of every k1_search launch
     {
         const int grid = c->k1_grid;
         ScopedTimer t(c, s_srch, T_SEARCH);
@@ -595,9 +632,8 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
     }
-    CU(c, wait_map_readers(c, s, c->s_main));  // k23_intra below overwrites this key frame's maps and list
+    CU(c, wait_map_readers(c, s));  // k23_intra below overwrites this key frame's maps and list (k1_fuse zeroes meta->valid_count)
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
-    CU(c, cudaMemsetAsync(&s->meta->valid_count, 0, sizeof(int), c->s_main));
     {
         ScopedTimer t(c, c->s_main, T_FUSE);
         FuseArgs F;
@@ -623,14 +659,14 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         dim3 grd((c->W + K23_TW - 1) / K23_TW, (c->H + K23_TH - 1) / K23_TH);
         k23_intra<true, true><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
     }
-    // the scratch planes go back to all-zero for the next key frame that uses buffers [hb]
-    CU(c, cudaMemsetAsync(c->tmp_depth[hb], 0, fplane, c->s_main));
-    CU(c, cudaMemsetAsync(c->tmp_sigma[hb], 0, fplane, c->s_main));
-    CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
-    c->hypfree_valid[hb] = true;
     CU(c, cudaGetLastError());
     CU(c, cudaEventRecord(s->ev_sd, c->s_main));
-    s->sd_recorded = true;
+    record_maps(c, s);
+    // the scratch planes (one allocation per buffer: depth | sigma) go back to all-zero for the next key frame that uses
+    // buffers [hb] -- after the maps-ready record, so not on this key frame's dependency chain
+    CU(c, cudaMemsetAsync(c->tmp_depth[hb], 0, 2 * fplane, c->s_main));
+    CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
+    c->hypfree_valid[hb] = true;
     s->has_semidense = true;
     s->vlist_ok = true;
     s->vlist_from_import = false;
@@ -655,6 +691,8 @@ static int interkf_common(sd_ctx* c, int kf_id, const int* nbr_ids, int n, bool 
     A.vlist = s->vlist;
     A.vcount = &s->meta->valid_count;
     const bool inplace = c->P.interkf_inplace != 0;
+    c->dirty = true;
+    const Slot* latest_sd = s;  // K4 reads the maps of kf and of its neighbours: wait for the last of them to be ready
     for (int j = 0; j < n; ++j) {
         Slot* nb = find(c, nbr_ids[j]);
         if (!nb) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown neighbour key frame %d", nbr_ids[j]);
@@ -667,9 +705,9 @@ static int interkf_common(sd_ctx* c, int kf_id, const int* nbr_ids, int n, bool 
         // earlier on this same stream, so the read is ordered after it
         N.depth = (inplace && nb->has_checked && nb != s) ? nb->depth_chk : nb->depth;
         N.sigma = nb->sigma;
-        if (nb->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, nb->ev_sd, 0));
+        if (nb->sd_seq > latest_sd->sd_seq) latest_sd = nb;
     }
-    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_sd, 0));
+    CU(c, wait_maps(c->s_chk, c->chk_seen_sd, latest_sd));
     if (s->dn_pending) {
         CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_dn, 0));
         s->dn_pending = false;
@@ -704,12 +742,9 @@ static int interkf_common(sd_ctx* c, int kf_id, const int* nbr_ids, int n, bool 
     }
     CU(c, cudaGetLastError());
     {   // this launch read the maps of kf and of its neighbours: writers of those maps wait for it
-        const long long idx = c->ring_i++;
-        CU(c, cudaEventRecord(c->ev_ring[idx % sd_ctx::RING], c->s_chk));
-        s->rd_idx = idx;
-        for (int j = 0; j < n; ++j) find(c, nbr_ids[j])->rd_idx = idx;
-        CU(c, cudaEventRecord(s->ev_chk, c->s_chk));
-        s->chk_recorded = true;
+        CU(c, record_chk(c, s));
+        s->rd_idx = s->chk_idx;
+        for (int j = 0; j < n; ++j) find(c, nbr_ids[j])->rd_idx = s->chk_idx;
     }
     s->has_checked = true;
     s->has_points = with_points;
@@ -728,7 +763,8 @@ int sd_update_pointset(sd_ctx* c, int kf_id) {
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     CU(c, cudaSetDevice(c->device));
     if (!s->points) CU(c, cudaMalloc(&s->points, (size_t)c->W * c->H * 3 * sizeof(float)));
-    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_sd, 0));
+    c->dirty = true;
+    CU(c, wait_maps(c->s_chk, c->chk_seen_sd, s));
     if (s->dn_pending) {
         CU(c, cudaStreamWaitEvent(c->s_chk, s->ev_dn, 0));
         s->dn_pending = false;
@@ -745,8 +781,7 @@ int sd_update_pointset(sd_ctx* c, int kf_id) {
         k5_pointset<<<grd, 256, 0, c->s_chk>>>(A);
     }
     CU(c, cudaGetLastError());
-    CU(c, cudaEventRecord(s->ev_chk, c->s_chk));
-    s->chk_recorded = true;
+    CU(c, record_chk(c, s));
     s->has_points = true;
     s->pose_changed = false;
     return SD_OK;
@@ -778,7 +813,8 @@ int sd_confident_points_device(sd_ctx* c, int kf_id, double max_sigma, int max_p
         c->conf_cap = cap;
     }
     cudaStream_t st = c->s_chk;
-    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(st, s->ev_sd, 0));
+    c->dirty = true;
+    CU(c, wait_maps(st, c->chk_seen_sd, s));
     ConfArgs A;
     A.P.W = c->W; A.P.H = c->H; A.P.pitch_f = c->pitch_f;
     A.P.fx = s->K[0]; A.P.fy = s->K[1]; A.P.cx = s->K[2]; A.P.cy = s->K[3];
@@ -814,8 +850,7 @@ int sd_confident_points_device(sd_ctx* c, int kf_id, double max_sigma, int max_p
     CU(c, cudaGetLastError());
     CU(c, cudaMemcpyAsync(&c->h_conf[0], &c->conf_state->total, sizeof(int), cudaMemcpyDeviceToHost, st));
     CU(c, cudaMemcpyAsync(&c->h_conf[1], &c->conf_state->confident, sizeof(int), cudaMemcpyDeviceToHost, st));
-    CU(c, cudaEventRecord(s->ev_chk, st));
-    s->chk_recorded = true;
+    CU(c, record_chk(c, s));
     CU(c, cudaStreamSynchronize(st));
     *count = c->h_conf[0];
     c->conf_last_xyz = A.out_xyz; c->conf_last_sigma = A.out_sigma; c->conf_last_pix = A.out_pix; c->conf_last_count = c->h_conf[0];
@@ -859,8 +894,9 @@ int sd_download_async(sd_ctx* c, int kf_id, float* depth, float* sigma, float* p
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     if (points && !s->has_points) return fail(c, SD_ERR_NOT_READY, "key frame %d has no point set", kf_id);
     CU(c, cudaSetDevice(c->device));
-    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_sd, 0));
-    if (s->chk_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_chk, 0));
+    c->dirty = true;
+    CU(c, wait_maps(c->s_dn, c->dn_seen_sd, s));
+    CU(c, wait_ring(c, c->s_dn, c->dn_seen_chk, s->chk_idx));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
     if (depth) CU(c, cudaMemcpy2DAsync(depth, wb, s->has_checked ? s->depth_chk : s->depth, pb, wb, c->H, cudaMemcpyDeviceToHost, c->s_dn));
     if (sigma) CU(c, cudaMemcpy2DAsync(sigma, wb, s->sigma, pb, wb, c->H, cudaMemcpyDeviceToHost, c->s_dn));
@@ -902,8 +938,9 @@ int sd_download_compact_async(sd_ctx* c, int kf_id, int with_points, int capacit
         CU(c, cudaEventCreateWithFlags(&ps.ev_cnt, cudaEventDisableTiming));
     }
     // stream order on s_dn: the copy of this slot's previous use precedes the kernel below
-    if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_sd, 0));
-    if (s->chk_recorded) CU(c, cudaStreamWaitEvent(c->s_dn, s->ev_chk, 0));
+    c->dirty = true;
+    CU(c, wait_maps(c->s_dn, c->dn_seen_sd, s));
+    CU(c, wait_ring(c, c->s_dn, c->dn_seen_chk, s->chk_idx));
     PackArgs A;
     A.W = c->W; A.pitch_f = c->pitch_f;
     A.vlist = s->vlist; A.vcount = &s->meta->valid_count;
@@ -1007,8 +1044,9 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
     // a re-upload of this key frame (or a recycled slot) forgets the slot's reader bookkeeping and makes only s_up
     // wait for the work still queued on the other streams: order the overwrite of the maps after that upload
-    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
-    CU(c, wait_map_readers(c, s, c->s_main));
+    c->dirty = true;
+    CU(c, wait_upload(c->s_main, c->main_seen_up, s));
+    CU(c, wait_map_readers(c, s));
     if (s->dn_pending) {
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
@@ -1016,7 +1054,7 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     CU(c, cudaMemcpy2DAsync(s->depth, pb, depth_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     CU(c, cudaMemcpy2DAsync(s->sigma, pb, sigma_dev, wb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     CU(c, cudaEventRecord(s->ev_sd, c->s_main));
-    s->sd_recorded = true;
+    record_maps(c, s);
     s->has_semidense = true;
     s->has_checked = false;
     s->vlist_ok = false;
@@ -1029,8 +1067,9 @@ int sd_import_maps_host(sd_ctx* c, int kf_id, const float* depth, const float* s
     if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", kf_id);
     CU(c, cudaSetDevice(c->device));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
-    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
-    CU(c, wait_map_readers(c, s, c->s_main));
+    c->dirty = true;
+    CU(c, wait_upload(c->s_main, c->main_seen_up, s));
+    CU(c, wait_map_readers(c, s));
     if (s->dn_pending) {
         CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
         s->dn_pending = false;
@@ -1038,8 +1077,8 @@ int sd_import_maps_host(sd_ctx* c, int kf_id, const float* depth, const float* s
     CU(c, cudaMemcpy2DAsync(s->depth, pb, depth, wb, wb, c->H, cudaMemcpyHostToDevice, c->s_main));
     CU(c, cudaMemcpy2DAsync(s->sigma, pb, sigma, wb, wb, c->H, cudaMemcpyHostToDevice, c->s_main));
     CU(c, cudaEventRecord(s->ev_sd, c->s_main));
+    record_maps(c, s);
     CU(c, cudaStreamSynchronize(c->s_main));  // the host buffers are borrowed for the call only
-    s->sd_recorded = true;
     s->has_semidense = true;
     s->has_checked = false;
     s->has_points = false;
@@ -1150,6 +1189,7 @@ int sd_halo_exchange(sd_ctx* c, const SdHaloPeer* peers, int n_peers) {
     if (!c->nccl_comm) return fail(c, SD_ERR_NOT_READY, "sd_halo_exchange: no communicator (sd_comm_init)");
     NcclApi* api = nccl_api();
     CU(c, cudaSetDevice(c->device));
+    c->dirty = true;
     const size_t plane = (size_t)c->pitch_f * c->H;  // whole pitched planes: every rank of a run has the same geometry
     // order the receives after everything that may still read (or is still producing) the planes they overwrite
     for (int p = 0; p < n_peers; ++p) {
@@ -1161,13 +1201,13 @@ int sd_halo_exchange(sd_ctx* c, const SdHaloPeer* peers, int n_peers) {
             Slot* s = find(c, P.send_ids[i]);
             if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", P.send_ids[i]);
             if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps to send", P.send_ids[i]);
-            if (s->sd_recorded) CU(c, cudaStreamWaitEvent(c->s_main, s->ev_sd, 0));
+            // the maps to send were produced on s_main itself (k23_intra / an earlier import): already in stream order
         }
         for (int i = 0; i < P.n_recv; ++i) {
             Slot* s = find(c, P.recv_ids[i]);
             if (!s) return fail(c, SD_ERR_UNKNOWN_KEYFRAME, "unknown key frame %d", P.recv_ids[i]);
-            CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
-            CU(c, wait_map_readers(c, s, c->s_main));
+            CU(c, wait_upload(c->s_main, c->main_seen_up, s));
+            CU(c, wait_map_readers(c, s));
             if (s->dn_pending) {
                 CU(c, cudaStreamWaitEvent(c->s_main, s->ev_dn, 0));
                 s->dn_pending = false;
@@ -1194,7 +1234,7 @@ int sd_halo_exchange(sd_ctx* c, const SdHaloPeer* peers, int n_peers) {
         for (int i = 0; i < P.n_recv; ++i) {
             Slot* s = find(c, P.recv_ids[i]);
             CU(c, cudaEventRecord(s->ev_sd, c->s_main));
-            s->sd_recorded = true;
+            record_maps(c, s);
             s->has_semidense = true;
             s->has_checked = false;
             s->has_points = false;
@@ -1282,7 +1322,7 @@ int sd_export_maps(sd_ctx* c, int kf_id, float* depth_dev, float* sigma_dev) {
     if (!s->has_semidense) return fail(c, SD_ERR_NOT_READY, "key frame %d has no semi-dense maps", kf_id);
     CU(c, cudaSetDevice(c->device));
     const size_t wb = (size_t)c->W * sizeof(float), pb = (size_t)c->pitch_f * sizeof(float);
-    CU(c, cudaStreamWaitEvent(c->s_main, s->ev_up, 0));
+    c->dirty = true;
     CU(c, cudaMemcpy2DAsync(depth_dev, wb, s->depth, pb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     CU(c, cudaMemcpy2DAsync(sigma_dev, wb, s->sigma, pb, wb, c->H, cudaMemcpyDeviceToDevice, c->s_main));
     return SD_OK;

@@ -31,8 +31,8 @@ struct KfMeta {  // device-resident per key frame
     unsigned long long sumsq;  // sum of squared grey levels
     float istddev;             // KeyFrame::I_stddev
     int active_count;          // entries in the active-pixel list
-    unsigned int k1_task;      // next 32-entry task of the running k1_search launch (zeroed before each launch)
-    int valid_count;           // entries in the valid-pixel list written by k23_intra (zeroed before each launch)
+    unsigned int k1_task;      // next 32-entry task of the running k1_search launch (zero between launches: the last warp out resets it)
+    int valid_count;           // entries in the valid-pixel list written by k23_intra (zeroed by the k1_fuse launch before it)
     unsigned int k0_ticket;    // blocks of k0_gradient that have added their sums (the last one computes istddev)
 };
 
@@ -61,6 +61,8 @@ struct SearchArgs {
     float chi_fuse;  // smallest float >= 5.99: `chi < 5.99` (float vs double literal) == `chi < chi_fuse`
     double mind_d, maxd_d;    // the same as doubles (gemm alpha)
     double inv_THETA, THETA;  // 1/THETA and THETA (PM.h:47) as doubles
+    float inv_theta_f;        // (float)inv_THETA
+    const float* ray;         // normalised image coordinates of the key frame: ray[x] = (x - cx) / fx, ray[W + y] = (y - cy) / fy (k0_gradient)
     const uint8_t* img;
     const float* grad;
     const float* theta;
@@ -68,7 +70,7 @@ struct SearchArgs {
     const uint32_t* list;
     const KfMeta* meta;
     int count_override;  // >= 0: use instead of meta->active_count (probes)
-    unsigned int* task_counter;  // zeroed before the launch; warps draw 32-entry tasks from it
+    unsigned int* task_counter;  // zero at launch; warps draw 32-entry tasks from it and the last warp to leave zeroes it again
     float2* hyp;       // nullable; hypothesis buffer [neighbour][hyp_stride]: (rho, sigma), or (-1, 0) for none
     int hyp_stride;
     float* probe_out;  // nullable; [entry][6] = {rho, sigma, best uj, supported, best_u, best_v} of neighbour 0
@@ -187,7 +189,8 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, K0_MIN_BLOCKS) k0_gradient(const
                                                             float* __restrict__ grad, float* __restrict__ theta, int pitch_f,
                                                             uint32_t* __restrict__ arc, int arc_pitch, uint4* __restrict__ rec,
                                                             uint32_t* __restrict__ list, KfMeta* __restrict__ meta,
-                                                            float lambdaG, float lambdaTheta, int border) {
+                                                            float lambdaG, float lambdaTheta, int border,
+                                                            float* __restrict__ ray, float fx, float fy, float cx, float cy) {
     __shared__ uint8_t tile[K0_TY + 3][K0_TW + 8];  // column c <-> x0 - 1 + c; row r <-> clamp(y0 - 1 + r)
     __shared__ float s_g[K0_TY + 1][K0_TW];          // GradImg of the tile rows and of the row below the tile (records)
     __shared__ uint32_t s_memb[K0_TY][K0_TW];        // per pixel: bit s = member of arc plane s
@@ -198,6 +201,11 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, K0_MIN_BLOCKS) k0_gradient(const
     const int tx = threadIdx.x, ty = threadIdx.y;
     const int tid = ty * K0_TX + tx;
     const int x0 = blockIdx.x * K0_TW, y0 = blockIdx.y * K0_TY;
+
+    // normalised image coordinates xp = K^-1 (x, y, 1) (PM.cc:862, 893), once per column / row instead of once per
+    // (pixel, neighbour) in k1_search and once per pixel in k4_inter_check: the same two IEEE operations, (x - cx) / fx
+    if (blockIdx.y == 0 && tid < K0_TW && x0 + tid < W) ray[x0 + tid] = ((float)(x0 + tid) - cx) / fx;
+    if (blockIdx.x == 0 && tid < K0_TY && y0 + tid < H) ray[W + y0 + tid] = ((float)(y0 + tid) - cy) / fy;
 
     if (x0 + K0_TW < W) {
         // interior columns: the 128 tile bytes of a row are 32 aligned words (x0 and the pitch are multiples of 128),
@@ -611,7 +619,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     uint32_t* tie = bestu + 32;                                    // per owner lane: two best errs too close for the float shortcut
     uint32_t* s_rng = tie + 32;                                    // per lane: u_lo | (u_hi + 1) << 16 -- parked for phase (D), which is register-lean
     const float colsf = (float)A.W;
-    const float inv_theta_f = (float)A.inv_THETA;
+    const float inv_theta_f = A.inv_theta_f;
     const size_t arc_plane = (size_t)A.H * A.arc_pitch;
 
   // persistent warps: the grid is sized to the machine; every warp draws (32 list entries x 1 neighbour)
@@ -620,13 +628,20 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
   // pixel's work) that the last warps to finish do not leave the machine idle for long.
   const unsigned nblk = ((unsigned)count + 31u) >> 5;
   const unsigned ntask = nblk * (unsigned)A.n;  // < 2^31: planes hold < 2^30 pixels (checked at upload), n <= 40
+  int j = 0;             // neighbour of the current task: a warp's tickets only grow, so j = task / nblk is tracked by
+  unsigned jbase = 0;    // stepping (jbase = j * nblk) instead of an integer division per task
   for (;;) {
     unsigned task = 0;
     if (lane == 0) task = atomicAdd(A.task_counter, 1u);
     task = __shfl_sync(full, task, 0);
-    if (task >= ntask) break;
-    const int j = (int)(task / nblk);
-    const int entry = (int)(task - (unsigned)j * nblk) * 32 + lane;
+    if (task >= ntask) {
+        // every warp of the grid draws exactly one ticket >= ntask (the one it leaves on); the warp that draws the last
+        // of them knows no other draw can follow and puts the counter back to zero for the next launch
+        if (lane == 0 && task == ntask + gridDim.x * (unsigned)K1_WARPS - 1u) *A.task_counter = 0u;
+        break;
+    }
+    while (task - jbase >= nblk) { ++j; jbase += nblk; }
+    const int entry = (int)(task - jbase) * 32 + lane;
     const bool valid = entry < count;
 
     int x = 0, y = 0;
@@ -643,7 +658,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         g1 = __uint_as_float(own.y);
         th1 = __uint_as_float(own.x);
     }
-    const float xp0 = (xf - A.cx) / A.fx, xp1 = (yf - A.cy) / A.fy;                   // PM.cc:893, 862
+    const float xp0 = __ldg(A.ray + x), xp1 = __ldg(A.ray + A.W + y);                 // (x - cx) / fx, (y - cy) / fy: PM.cc:893, 862
 
     {
         const NbrConst& N = A.nb[j];
@@ -878,10 +893,10 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
             best_u = ustar;  // PM.cc:459
             const float istd = N.meta->istddev;
             const float uvar = 2 * istd * istd / den;  // PM.cc:457
-            // ComputeInvDepthHypothesis (xp recomputed from the list entry with the arithmetic of phase (A))
+            // ComputeInvDepthHypothesis (xp reloaded through the list entry: phase (A)'s values are not kept alive)
             const uint32_t ent = A.list[entry];
-            const double xp0d = (double)(((float)(int)(ent & 0xffffu) - A.cx) / A.fx);
-            const double xp1d = (double)(((float)(int)(ent >> 16) - A.cy) / A.fy);
+            const double xp0d = (double)__ldg(A.ray + (ent & 0xffffu));
+            const double xp1d = (double)__ldg(A.ray + A.W + (ent >> 16));
             const double d2 = N.Rd2[2] + __fma_rn(N.Rd2[1], xp1d, N.Rd2[0] * xp0d);
             const double d0 = N.Rd0[2] + __fma_rn(N.Rd0[1], xp1d, N.Rd0[0] * xp0d);
             const float num2f = (float)(d0 * (double)A.fx);
@@ -914,7 +929,7 @@ struct FuseArgs {
     float chi_fuse;
     const float2* hyp;
     const uint32_t* list;
-    const KfMeta* meta;
+    KfMeta* meta;  // active_count is read; valid_count is zeroed for the k23_intra launch that follows on the same stream
     float* depth;
     float* sigma;
 };
@@ -922,6 +937,7 @@ struct FuseArgs {
 template <int NT>
 __global__ void __launch_bounds__(128, K1F_MIN_BLOCKS) k1_fuse(const FuseArgs F) {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e == 0) F.meta->valid_count = 0;
     if (e >= F.meta->active_count) return;
     float hd[NT], hs[NT];
     unsigned long long present = 0;
@@ -965,6 +981,7 @@ __global__ void __launch_bounds__(K1FR_THREADS) k1_fuse_rows(const FuseArgs F) {
     float* ss = k1fr_smem + n * T + tid;                                         // ss[j * T]: sigma
     unsigned char* sc = reinterpret_cast<unsigned char*>(k1fr_smem + 2 * n * T) + tid;  // sc[j * T]: compatible hypotheses so far
     const int e = blockIdx.x * T + tid;
+    if (e == 0) F.meta->valid_count = 0;
     if (e >= F.meta->active_count) return;
     const float thr = F.chi_fuse, thr_lo = thr * (1.0f - 1e-5f), thr_hi = thr * (1.0f + 1e-5f);
     unsigned long long present = 0;

@@ -98,6 +98,50 @@ def test_compact_download_async_ring_and_loop(pkg, po, synth, pipeline):
     ctx.close()
 
 
+def test_back_to_back_passes_without_sync(pkg, po, synth, pipeline):
+    """bench.py's step, three times with NO host synchronisation in between and different images every time: upload of
+    all key frames (the planes of the previous pass are still being read), sd_semidense_loop with compact downloads.
+    Every cross-stream dependency is a single wait on the latest record needed (upload / maps-ready / K4 numbers):
+    a missing one shows up as planes of the wrong pass.  The last pass must equal the oracle on ITS images."""
+    import torch
+    nkf, n = 14, 5
+    scenes = [synth.Scene(SMALL_CAM, seed=s) for s in (61, 62, 63)]
+    plans = [pipeline.SequencePlan(sc, nkf, n) for sc in scenes]
+    cap = (scenes[0].w - 4) * (scenes[0].h - 4)
+    ctx = pkg.Context(0)
+    host = [torch.from_numpy(np.stack([sc.render(k) for k in pl.ids])).pin_memory() for sc, pl in zip(scenes, plans)]
+    recs = torch.zeros((3, nkf, cap * pkg.COMPACT_POINT.itemsize), dtype=torch.uint8).pin_memory()
+    counts = torch.full((3, nkf), -1, dtype=torch.int32).pin_memory()
+    loops = [ctx.make_loop([dict(kf_id=k, nbrs=pl.nbrs[k], rots=pl.rots[k], prior=pl.prior[k],
+                                 download=(pkg.SD_DL_COMPACT_POINTS, recs[r, i].data_ptr(), cap, counts[r, i:].data_ptr()))
+                            for i, k in enumerate(pl.ids)]) for r, pl in enumerate(plans)]
+    for r, (sc, pl) in enumerate(zip(scenes, plans)):
+        for i, k in enumerate(pl.ids):
+            ctx.upload_keyframe_ptr(k, host[r][i].data_ptr(), sc.w, sc.h, sc.w, sc.K, pl.poses[k], device=False)
+        assert ctx.semidense_loop(loops[r]).all()
+    ctx.sync()
+    for r, (sc, pl) in enumerate(zip(scenes, plans)):
+        images = {k: host[r][i].numpy() for i, k in enumerate(pl.ids)}
+        ora = run_oracle(po, pl, images)
+        for i, k in enumerate(pl.ids):
+            m = int(counts[r, i])
+            assert 0 < m <= cap
+            d, s, p = pkg.expand_compact(recs[r, i].numpy().view(pkg.COMPACT_POINT)[:m], sc.h, sc.w, points=True)
+            assert np.array_equal(d, ora.plane(k, po.DEPTH_CHECKED)), (r, k)
+            assert np.array_equal(s, ora.plane(k, po.SIGMA)), (r, k)
+            assert np.array_equal(p, ora.plane(k, po.POINTS)), (r, k)
+        if r == 2:   # the resident planes are the last pass's
+            for k in pl.ids:
+                assert np.array_equal(ctx.plane(k, po.DEPTH), ora.plane(k, po.DEPTH)), k
+    # the same key frame searched twice in a row without an upload in between (k1_search puts its task counter back itself)
+    k = plans[2].ids[6]
+    for _ in range(2):
+        ctx.semidense(k, plans[2].nbrs[k], plans[2].rots[k], *plans[2].prior[k])
+    assert np.array_equal(ctx.plane(k, po.DEPTH), ora.plane(k, po.DEPTH))
+    assert np.array_equal(ctx.plane(k, po.SIGMA), ora.plane(k, po.SIGMA))
+    ctx.close()
+
+
 def test_semidense_loop_dense_downloads_and_skips(pkg, po, synth, pipeline):
     """sd_semidense_loop with dense downloads; a list that lacks some neighbours skips their inter-KF stage like
     PM.cc:289-297 and says so."""
