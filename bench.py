@@ -135,6 +135,61 @@ class ClockSampler:
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
 
 
+class NvmlSampler:
+    """Per-rank clocks / power / throttle reasons of the rank's own GPU during the timed region, sampled in-process
+    through NVML (what nvidia-smi reads): cheap enough for every rank of an 8-GPU run to do it.  Rank 0 also runs the
+    recipe's nvidia-smi line (ClockSampler); this one is what `per_rank` reports."""
+
+    def __init__(self, torch, local):
+        self.h, self.nv, self.samples, self.stop_flag, self.t = None, None, [], False, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            pr = torch.cuda.get_device_properties(local)
+            bus = "%08x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+            self.h = pynvml.nvmlDeviceGetHandleByPciBusId(bus.encode())
+            self.nv = pynvml
+        except Exception:
+            self.h = None
+
+    def _run(self):
+        nv = self.nv
+        while not self.stop_flag:
+            try:
+                self.samples.append((nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM),
+                                     nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0,
+                                     nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)))
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        if self.h is None:
+            return
+        self.samples, self.stop_flag = [], False
+        self.t = threading.Thread(target=self._run, daemon=True)
+        self.t.start()
+
+    def stop(self):
+        if self.h is None or self.t is None:
+            return {"sm_mhz": None, "reasons": ["nvml unavailable"]}
+        self.stop_flag = True
+        self.t.join(timeout=2)
+        nv, reasons = self.nv, set()
+        names = {"hw_slowdown": "nvmlClocksEventReasonHwSlowdown", "hw_thermal_slowdown": "nvmlClocksEventReasonHwThermalSlowdown",
+                 "sw_thermal_slowdown": "nvmlClocksEventReasonSwThermalSlowdown", "sw_power_cap": "nvmlClocksEventReasonSwPowerCap",
+                 "hw_power_brake": "nvmlClocksEventReasonHwPowerBrakeSlowdown"}
+        for _, _, mask in self.samples:
+            for label, attr in names.items():
+                bit = getattr(nv, attr, None) or getattr(nv, attr.replace("ClocksEventReason", "ClocksThrottleReason"), 0)
+                if bit and (mask & bit):
+                    reasons.add(label)
+        sm = [x[0] for x in self.samples]
+        pw = [x[1] for x in self.samples]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_mhz_min": float(min(sm)) if sm else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
 def workload_name(args, world):
     return (f"{args.nkf} synthetic {args.camera} key frames per GPU (chris_logic_HD720 intrinsics), "
             f"{args.nbr} covisible neighbours" + (f", {world} ranks keyframe-sharded with NCCL map exchange" if world > 1 else ""))
@@ -334,11 +389,14 @@ class Workload:
                ("loop", ctx.make_loop([self._item(leg, k, finish_only=True) for k in boundary] + [self._item(leg, k) for k in interior]))]
         return ops
 
-    def step(self, leg):
+    def step(self, leg, mark=None):
+        """`mark(label)`, if given, is called after the uploads and after every op of the step (timeline pass)."""
         ctx, W, H, K = self.ctx, self.W, self.H, self.scene.K
         src, on_dev = (self.dev_img, True) if leg == "value" else (self.host_img, False)
         for k in self.resident:
             ctx.upload_keyframe_ptr(k, src[self.slot[k]].data_ptr(), W, H, W, K, self.poses[k], device=on_dev)
+        if mark:
+            mark("uploads_issued")
         for op, arg in self.loops[leg]:
             if op == "loop":
                 done = ctx.semidense_loop(arg)
@@ -346,6 +404,8 @@ class Workload:
                     raise RuntimeError("sd_semidense_loop skipped an inter-key-frame check")
             elif not os.environ.get("BENCH_SKIP_NCCL"):
                 ctx.halo_exchange(self.halo)
+            if mark:
+                mark(op)
 
     def bytes_per_step(self, leg):
         px = self.W * self.H
@@ -400,6 +460,9 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     host_issue_ms = {}
+    rank_ms = {}                       # this rank's own span per leg (the line's figures are the max over ranks)
+    nvml = NvmlSampler(torch, local)
+    rank_clocks = {}
 
     def timed(work, leg, steps, warmup, sampler=None):
         c = work.ctx
@@ -409,6 +472,8 @@ def run_b200(args):
         barrier()
         if sampler:
             sampler.start()
+        if leg in ("value", "e2e"):
+            nvml.start()
         l0 = c.launch_count()
         c.span_begin()
         t_host = time.perf_counter()
@@ -416,9 +481,12 @@ def run_b200(args):
             work.step(leg)
         host_issue_ms[leg] = 1e3 * (time.perf_counter() - t_host) / steps   # host time to ISSUE a step (no device wait)
         ms = c.span_end()
+        if leg in ("value", "e2e"):
+            rank_clocks[leg] = nvml.stop()
         barrier()
         clocks = sampler.stop() if sampler else None
         launches = c.launch_count() - l0
+        rank_ms[leg] = ms / steps
         t = torch.tensor([ms], dtype=torch.float64, device=dev)
         if os.environ.get("BENCH_VERBOSE"):
             sys.stderr.write(f"rank {rank}: numa cpus {numa}; {leg}: span {ms:.2f} ms for {steps} steps, host issue {host_issue_ms[leg]:.2f} ms/step\n")
@@ -459,6 +527,35 @@ def run_b200(args):
 
     kf_total_per_step = args.nkf * world
     rate = {leg: kf_total_per_step * args.steps / (ms[leg] * 1e-3) for leg in LEGS}
+
+    # one more pass of the value step with CUDA events on the compute stream (fusion / intra stage / NCCL) after every
+    # op: when the boundary key frames' maps are ready, when the exchange has completed, when the last map is ready
+    timeline = None
+    if world > 1:
+        st = torch.cuda.ExternalStream(ctx.compute_stream(), device=dev)
+        marks = []
+
+        def mark(label):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record(st)
+            marks.append((label, e, time.perf_counter()))
+        ctx.sync()
+        barrier()
+        t_host0 = time.perf_counter()
+        mark("start")
+        wl.step("value", mark=mark)
+        ctx.sync()
+        labels = ["start", "uploads_issued", "boundary_maps_ready", "exchange_done", "last_map_ready"]
+        timeline = {"stream": "compute stream (k1_fuse, k23_intra, NCCL send/recv); K4 and the search run on their own streams",
+                    "device_ms": {lab: round(marks[0][1].elapsed_time(m[1]), 3) for lab, m in zip(labels, marks)},
+                    "host_issue_ms": {lab: round(1e3 * (m[2] - t_host0), 3) for lab, m in zip(labels, marks)}}
+
+    mine = {"rank": rank, "timeline": timeline, "ms_per_step": {k: round(v, 3) for k, v in rank_ms.items()},
+            "host_issue_ms_per_step": {k: round(v, 3) for k, v in host_issue_ms.items()}, "clocks": rank_clocks, "numa_cpus": numa}
+    per_rank = [mine]
+    if world > 1:
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
 
     seam = None
     if world > 1 and not args.no_seam_check:
@@ -525,6 +622,9 @@ def run_b200(args):
             "kernels_standalone_us": alone_us,
             "kernels_standalone_share": {k: v / max(sum(alone_us.values()), 1e-9) for k, v in alone_us.items()},
             "valid_fraction": valid_fraction,
+            # every rank's own span (the headline figures are the max over ranks), its host issue time and the clocks /
+            # power / throttle reasons of ITS GPU during the value and e2e legs: tells GPU-to-GPU variance from a schedule effect
+            "per_rank": per_rank,
         }
         if seam is not None:
             line["seam_parity"] = seam

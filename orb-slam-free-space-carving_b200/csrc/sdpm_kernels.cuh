@@ -452,6 +452,13 @@ __device__ __forceinline__ int line_row(float ab, float cb, float uf, float& vf)
     vf = __fadd_rn(__fmul_rn(ab, uf), cb);
     return __float_as_int(__fadd_rz(-vf, 12582912.0f)) - 0x4B400000;
 }
+// the same, also returning the magic sum t = 1.5*2^23 + row as a float: for an admissible row, t - (1.5*2^23 - 1) is
+// (float)row + 1 exactly (all three are integers below 2^24)
+__device__ __forceinline__ int line_row(float ab, float cb, float uf, float& vf, float& t) {
+    vf = __fadd_rn(__fmul_rn(ab, uf), cb);
+    t = __fadd_rz(-vf, 12582912.0f);
+    return __float_as_int(t) - 0x4B400000;
+}
 __device__ __forceinline__ int line_row(float ab, float cb, int u) {
     float vf;
     return line_row(ab, cb, small_int_to_float(u), vf);
@@ -572,7 +579,10 @@ __device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const flo
 constexpr int K1_WARPS = K1_WARPS_PER_BLOCK;
 constexpr int K1_QHALF = 512;           // what 16 lanes can queue in one scan step (16 lanes x 32 columns)
 constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller step is queued in two halves
-constexpr int K1_WARP_SMEM = 512 + 256 + 4 * K1_QCAP + 4 * 128;  // 3 456 bytes per warp
+constexpr int K1_WARP_SMEM = 512 + 256 + 4 * K1_QCAP + 4 * 128 + 16;  // 3 472 bytes per warp
+#ifndef K1_ATOMIC_QUEUE
+#define K1_ATOMIC_QUEUE 1  // queue positions from one shared-memory atomicAdd per lane instead of a five-step shuffle scan
+#endif
 #ifndef K1F_MIN_BLOCKS
 #define K1F_MIN_BLOCKS 8
 #endif
@@ -618,6 +628,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     uint32_t* bestu = beste + 32;
     uint32_t* tie = bestu + 32;                                    // per owner lane: two best errs too close for the float shortcut
     uint32_t* s_rng = tie + 32;                                    // per lane: u_lo | (u_hi + 1) << 16 -- parked for phase (D), which is register-lean
+    uint32_t* s_qn = s_rng + 32;                                   // the queue length `qn` as the lanes' atomicAdd sees it (K1_ATOMIC_QUEUE)
     const float colsf = (float)A.W;
     const float inv_theta_f = A.inv_theta_f;
     const size_t arc_plane = (size_t)A.H * A.arc_pitch;
@@ -718,6 +729,9 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
         s_rng[lane] = (uint32_t)(u_lo & 0xffff) | ((uint32_t)(u_hi + 1) << 16);  // 0 <= u_lo <= W, -1 <= u_hi <= W
         beste[lane] = 0x7f800000u;  // +inf
         tie[lane] = 0;
+#if K1_ATOMIC_QUEUE
+        if (lane == 0) *s_qn = 0u;
+#endif
         __syncwarp();
 
         // ---------------- (C) evaluate queued candidates, one per lane ----------------
@@ -736,8 +750,8 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                     uq = (int)(e & 0xffffu);
                     const float4 p4 = par4[owner];
                     const float2 p2 = par2[owner];
-                    float vf;
-                    const int r0 = line_row(p4.x, p4.y, small_int_to_float(uq), vf);  // 0 < r0 < H by construction
+                    float vf, rt;
+                    const int r0 = line_row(p4.x, p4.y, small_int_to_float(uq), vf, rt);  // 0 < r0 < H by construction
                     const int xc = min(uq, A.W - 1);
                     // one record = orientation + both rows of both bilinear taps (second row clamped to the image, H2);
                     // requested before the gates are known (3 of 4 queued candidates pass them)
@@ -748,7 +762,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                     const float cur = __uint_as_float(beste[owner]);
                     if (orientation_gates(T2, p2.x, p2.y, A.lambdaL, A.lambdaTheta)) {
                         const float yv = -vf;
-                        const float w0 = (small_int_to_float(r0) + 1.0f) - yv;  // bilinear_col weights, PM.cc:46-53
+                        const float w0 = (rt - 12582911.0f) - yv;  // ((float)r0 + 1) - yv: bilinear_col weights, PM.cc:46-53
                         const float w1 = 1.0f - w0;
                         const float rI = p4.z - (i0 * w0 + i1 * w1);
                         const float rG = p4.w - (gg0 * w0 + gg1 * w1);
@@ -770,23 +784,59 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                     }
                 }
                 __syncwarp();
-                if (won && beste[owner] == eb) bestu[owner] = (uint32_t)uq;
+                // of the candidates that lowered an owner's best in this round, the one whose err is still the best owns bestu
+                const uint32_t now = won ? beste[owner] : ~eb;
+                if (now == eb) bestu[owner] = (uint32_t)uq;
+#if K1_ATOMIC_QUEUE
+                if (lane == 0) *s_qn = (uint32_t)base;  // what the next push's atomicAdd starts from
+#endif
                 __syncwarp();
                 qn = base;
             }
         };
 
         // ---------------- (B) run-by-run scan of the arc plane ----------------
+        // Queue positions.  K1_ATOMIC_QUEUE: every lane with candidates takes its slice of the queue with ONE shared-memory
+        // atomicAdd (s_qn mirrors qn) and the warp total is one REDUX -- ~6 instructions instead of the ~28 of a shuffle
+        // prefix sum.  The slices then come in arbitrary lane order, which no result depends on: the per-owner minimum is
+        // order-free, and of two candidates within the tie band of the final best the second to reach the atomicMin
+        // always sees the other one (or something between them) as `old` and flags the owner for the exact re-scan.
         auto push = [&](uint32_t m, int col_base) {
             const int cnt = __popc(m);
+            const uint32_t tag = ((uint32_t)lane << 16) | (uint32_t)col_base;
+#if K1_ATOMIC_QUEUE
+            const int total = __reduce_add_sync(full, cnt);
+            if (total <= K1_QHALF) {
+                if (m) {
+                    uint32_t* qp = queue + atomicAdd(s_qn, (uint32_t)cnt);
+                    do {  // two per trip, from the top bit down, branch-free: bfind (FLO) gives the index directly and is
+                          // 0xffffffff for m == 0, which shl.b32 clamps to a shift by 32, i.e. to 0 -- m stays 0
+                        uint32_t b0, b1, s0, s1;
+                        asm("bfind.u32 %0, %1;" : "=r"(b0) : "r"(m));
+                        asm("shl.b32 %0, 1, %1;" : "=r"(s0) : "r"(b0));
+                        m ^= s0;
+                        qp[0] = tag + b0;
+                        asm("bfind.u32 %0, %1;" : "=r"(b1) : "r"(m));
+                        asm("shl.b32 %0, 1, %1;" : "=r"(s1) : "r"(b1));
+                        if (m) qp[1] = tag + b1;
+                        m ^= s1;
+                        qp += 2;
+                    } while (m);
+                }
+                qn += total;
+                __syncwarp();
+                return;
+            }
+#endif
             int incl = cnt;
 #pragma unroll
             for (int dlt = 1; dlt < 32; dlt <<= 1) {
                 const int v = __shfl_up_sync(full, incl, dlt);
                 if (lane >= dlt) incl += v;
             }
+#if !K1_ATOMIC_QUEUE
             const int total = __shfl_sync(full, incl, 31);
-            const uint32_t tag = ((uint32_t)lane << 16) | (uint32_t)col_base;
+#endif
             int pos = qn + incl - cnt;
             if (total <= K1_QHALF) {
                 while (m) {
@@ -815,6 +865,9 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                         queue[pos++] = tag + (uint32_t)bit;
                     }
                 qn += total - half;
+#if K1_ATOMIC_QUEUE
+                if (lane == 0) *s_qn = (uint32_t)qn;
+#endif
                 __syncwarp();
             }
         };

@@ -72,3 +72,26 @@ def test_reference_arm_ignores_omp_num_threads_and_product_library(built):
     d = json.loads([ln for ln in r.stdout.splitlines() if ln.strip().startswith("{")][-1])
     assert d["cpu_baseline"]["cores"] == len(os.sched_getaffinity(0))
     assert "libpm_oracle.so" in r.stderr and "libsdpm.so" not in r.stderr
+
+
+def test_k1_traffic_profile_is_not_older_than_the_kernels():
+    """bench.py reads `roofline.traffic` and the issue-slot roofline's instruction count from profiles/k1_traffic.json
+    (ncu counters cannot be taken inside a timed run).  The file records the commit it was measured at; a kernel source
+    changed after that commit makes the figures stale, and this test fail, until the launch list is taken again
+    (tools/gpu_r02c.sh + tools/ncu_launch_summary.py --write-traffic)."""
+    import pytest
+    with open(os.path.join(ROOT, "profiles", "k1_traffic.json")) as f:
+        d = json.load(f)
+    assert d.get("commit"), "profiles/k1_traffic.json does not say which commit it was measured at"
+    assert d["dram_bytes_per_launch"] > 0 and d["warp_instructions_per_keyframe"] > 0
+    if not os.path.isdir(os.path.join(ROOT, ".git")):
+        pytest.skip("no git history here (GPU box snapshot)")
+    kernels = os.path.join("orb-slam-free-space-carving_b200", "csrc", "sdpm_kernels.cuh")
+    git = lambda *a: subprocess.run(["git", "-C", ROOT] + list(a), capture_output=True, text=True)
+    if git("cat-file", "-e", d["commit"] + "^{commit}").returncode != 0:
+        pytest.skip("the recorded commit is not in this clone")
+    last = git("log", "-1", "--format=%H", "--", kernels).stdout.strip()
+    assert last, "kernel source has no history"
+    assert git("merge-base", "--is-ancestor", last, d["commit"]).returncode == 0, \
+        f"{kernels} changed in {last[:8]}, after the profile's commit {d['commit'][:8]}: re-measure"
+    assert git("diff", "--quiet", "HEAD", "--", kernels).returncode == 0, f"{kernels} has uncommitted changes: the profile is stale"

@@ -24,5 +24,7 @@ P
 CMD="python bench.py --nkf 24 --steps 2 --warmup 1 --no-cpu-baseline --no-configs"
 timeout 900 ncu --metrics gpu__time_duration.sum,smsp__inst_executed.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -c 400 --csv \
     --log-file gpurun_out/${TAG}_launches.csv $CMD > gpurun_out/${TAG}_ncu_list.log 2>&1; echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:k1_search -s 30 -c 1 -f -o gpurun_out/${TAG}_k1_search $CMD > gpurun_out/${TAG}_ncu_k1.log 2>&1; echo "ncu k1 rc=$?"
+for k in ${NCU_KERNELS:-k1_search}; do
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:$k -s 30 -c 1 -f -o gpurun_out/${TAG}_$k $CMD > gpurun_out/${TAG}_ncu_$k.log 2>&1; echo "ncu $k rc=$?"
+done
 ls -la gpurun_out | head -40
