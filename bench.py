@@ -357,6 +357,18 @@ class Workload:
         self.counts = torch.zeros((len(self.owned),), dtype=torch.int32).pin_memory()
         self.oslot = {k: i for i, k in enumerate(self.owned)}
         self.halo = ctx.make_halo(shard.send, shard.recv) if world > 1 else None
+        # upload order = the order in which the step needs the planes: at world > 1 the boundary key frames are searched
+        # first, so their images and their neighbours' go first (a rank whose boundary is at the END of its range would
+        # otherwise run all its K0 launches alone before its first search, and its peer would wait for it at the exchange)
+        self.upload_order = list(self.resident)
+        if world > 1:
+            first, seen = [], set()
+            for k in sorted({k for ids in shard.send.values() for k in ids}):
+                for j in [k] + [int(x) for x in self.plan.nbrs[k]]:
+                    if j not in seen:
+                        seen.add(j)
+                        first.append(j)
+            self.upload_order = first + [k for k in self.resident if k not in seen]
         self.loops = {leg: self._make_loops(leg) for leg in legs}
 
     def _download(self, leg, k):
@@ -393,7 +405,7 @@ class Workload:
         """`mark(label)`, if given, is called after the uploads and after every op of the step (timeline pass)."""
         ctx, W, H, K = self.ctx, self.W, self.H, self.scene.K
         src, on_dev = (self.dev_img, True) if leg == "value" else (self.host_img, False)
-        for k in self.resident:
+        for k in self.upload_order:
             ctx.upload_keyframe_ptr(k, src[self.slot[k]].data_ptr(), W, H, W, K, self.poses[k], device=on_dev)
         if mark:
             mark("uploads_issued")

@@ -640,12 +640,9 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
         F.n = n; F.lambdaN = c->P.lambdaN; F.pitch_f = c->pitch_f; F.hyp_stride = c->hyp_stride; F.chi_fuse = c->chi_fuse_f;
         F.hyp = c->hyp[hb]; F.list = s->list; F.meta = s->meta; F.depth = c->tmp_depth[hb]; F.sigma = c->tmp_sigma[hb];
         const int blocks = ((c->W - 2 * c->P.border) * (c->H - 2 * c->P.border) + 127) / 128;  // the list's capacity
-#ifndef K1F_ROWS_MIN_N
-#define K1F_ROWS_MIN_N 17  // from this many neighbours on, the shared-memory-column variant (register arrays would spill)
-#endif
-        if (n < K1F_ROWS_MIN_N && n <= 6) k1_fuse<6><<<blocks, 128, 0, c->s_main>>>(F);
-        else if (n < K1F_ROWS_MIN_N && n <= 10) k1_fuse<10><<<blocks, 128, 0, c->s_main>>>(F);
-        else if (n < K1F_ROWS_MIN_N && n <= 16) k1_fuse<16><<<blocks, 128, 0, c->s_main>>>(F);
+        if (n <= 6) k1_fuse<6><<<blocks, 128, 0, c->s_main>>>(F);
+        else if (n <= 10) k1_fuse<10><<<blocks, 128, 0, c->s_main>>>(F);
+        else if (n <= 16) k1_fuse<16><<<blocks, 128, 0, c->s_main>>>(F);
         else {
             const int cap = (c->W - 2 * c->P.border) * (c->H - 2 * c->P.border);
             k1_fuse_rows<<<(cap + K1FR_THREADS - 1) / K1FR_THREADS, K1FR_THREADS, k1fr_smem_bytes(n), c->s_main>>>(F);
