@@ -19,6 +19,7 @@
 //
 // Plane reads use clamp-to-edge addressing wherever the reference can read out of bounds.
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -127,6 +128,36 @@ struct InterArgs {
 #define SD_EPS_F 9.99999997475242707878e-07f
 
 __device__ __forceinline__ int clampi(int v, int lo, int hi) { return v < lo ? lo : (v > hi ? hi : v); }
+
+// The two grey levels of a search record (this row | the row below): SD_REC_HALF packs them as two half floats -- every u8
+// is exact in fp16, and half -> float is ONE instruction on the packed word (HADD2.F32 with a half selector) instead of a
+// mask / shift, an OR and a subtraction each.
+#ifndef SD_REC_HALF
+#define SD_REC_HALF 1  // 0: two 16-bit integers (round 2's first layout); bench 3 722 -> 3 760 KF/s, K0 26 -> 24 us with halves
+#endif
+__device__ __forceinline__ uint32_t rec_pack_grey(int lo, int hi) {
+#if SD_REC_HALF
+    return (uint32_t)__half_as_ushort(__int2half_rn(lo)) | ((uint32_t)__half_as_ushort(__int2half_rn(hi)) << 16);
+#else
+    return (uint32_t)lo | ((uint32_t)hi << 16);
+#endif
+}
+__device__ __forceinline__ float small_int_to_float(int u);
+__device__ __forceinline__ float rec_grey_lo(uint32_t w) {
+#if SD_REC_HALF
+    return __low2float(*reinterpret_cast<const __half2*>(&w));
+#else
+    return small_int_to_float((int)(w & 0xffffu));
+#endif
+}
+__device__ __forceinline__ float rec_grey_hi(uint32_t w) {
+#if SD_REC_HALF
+    return __high2float(*reinterpret_cast<const __half2*>(&w));
+#else
+    return small_int_to_float((int)(w >> 16));
+#endif
+}
+
 
 // cv::fastAtan2 scalar, degrees in [0, 360]
 __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
@@ -249,7 +280,7 @@ __global__ void __launch_bounds__(K0_TX* K0_TY, K0_MIN_BLOCKS) k0_gradient(const
         float gx, gy;
         g[i] = sobel_mag(p00, p01, p02, p10, p12, p20, p21, p22, gx, gy);
         s_g[ty][c - 1] = g[i];
-        pk[i] = (uint32_t)p11 | ((uint32_t)p21 << 16);  // tile rows are clamped at load: p21 is row min(y + 1, H - 1)
+        pk[i] = rec_pack_grey(p11, p21);  // tile rows are clamped at load: p21 is row min(y + 1, H - 1)
         th[i] = fast_atan2_deg(gy, gx);
         const int x = xb + i;
         const bool on = (g[i] >= lambdaG) && x < W && y < H;
@@ -402,8 +433,8 @@ __device__ __forceinline__ void bilinear_rec(const uint4* __restrict__ rec, int 
     const int xc = clampi(uj, 0, W - 1);
     const uint4 r = __ldg(rec + (unsigned)(clampi(y0, 0, H - 1) * pitch + xc));
     const bool above = y0 < 0;
-    const float i0 = small_int_to_float((int)(r.w & 0xffffu));
-    const float i1 = above ? i0 : small_int_to_float((int)(r.w >> 16));
+    const float i0 = rec_grey_lo(r.w);
+    const float i1 = above ? i0 : rec_grey_hi(r.w);
     const float g0 = __uint_as_float(r.y);
     const float g1 = above ? g0 : __uint_as_float(r.z);
     vI = i0 * w0 + i1 * w1;
@@ -574,8 +605,8 @@ __device__ __forceinline__ bool fuse_hypotheses(const float (&hd)[NT], const flo
 }
 
 #ifndef K1_WARPS_PER_BLOCK
-#define K1_WARPS_PER_BLOCK 8
-#endif
+#define K1_WARPS_PER_BLOCK 4  // 4-warp blocks, 12 per SM: the same 48 resident warps as 8 x 6, but a retiring block frees its
+#endif                      // registers for the waiting short kernels twice as early (bench +0.5 %)
 constexpr int K1_WARPS = K1_WARPS_PER_BLOCK;
 constexpr int K1_QHALF = 512;           // what 16 lanes can queue in one scan step (16 lanes x 32 columns)
 constexpr int K1_QCAP = K1_QHALF + 32;  // on top of < 32 leftovers; a fuller step is queued in two halves
@@ -590,7 +621,7 @@ constexpr int K1_WARP_SMEM = 512 + 256 + 4 * K1_QCAP + 4 * 128 + 16;  // 3 472 b
 #define K4_MIN_BLOCKS 8
 #endif
 #ifndef K1_MIN_BLOCKS
-#define K1_MIN_BLOCKS 6
+#define K1_MIN_BLOCKS 12
 #endif
 #define K1_TIE_REL 2e-6f            // float shortcut of err: two candidates closer than this are re-scanned exactly
 #define K1_ERR_LIMIT_LO 999000.0f   // PM.cc:437 initial best_match_err = 1e6
@@ -665,7 +696,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
     float I1 = 0.f, g1 = 0.f, th1 = 0.f;
     if (valid) {  // the pixel's own record: intensity (PM.cc:202), GradImg (PM.cc:434), GradTheta (PM.cc:214)
         const uint4 own = __ldg(A.rec + (unsigned)(y * A.pitch_f + x));
-        I1 = small_int_to_float((int)(own.w & 0xffffu));
+        I1 = rec_grey_lo(own.w);
         g1 = __uint_as_float(own.y);
         th1 = __uint_as_float(own.x);
     }
@@ -758,7 +789,7 @@ __global__ void __launch_bounds__(K1_WARPS * 32, K1_MIN_BLOCKS) k1_search(const 
                     const uint4 rc = __ldg(N.rec + (unsigned)(r0 * A.pitch_f + xc));  // planes hold < 2^31 elements (checked at upload)
                     const float T2 = __uint_as_float(rc.x);
                     const float gg0 = __uint_as_float(rc.y), gg1 = __uint_as_float(rc.z);
-                    const float i0 = small_int_to_float((int)(rc.w & 0xffffu)), i1 = small_int_to_float((int)(rc.w >> 16));
+                    const float i0 = rec_grey_lo(rc.w), i1 = rec_grey_hi(rc.w);
                     const float cur = __uint_as_float(beste[owner]);
                     if (orientation_gates(T2, p2.x, p2.y, A.lambdaL, A.lambdaTheta)) {
                         const float yv = -vf;
