@@ -590,6 +590,8 @@ def run_b200(args):
                 prof = json.load(f)
         except Exception:
             pass
+        if (prof.get("camera", "720p"), int(prof.get("neighbours", 10))) != (args.camera, n):
+            prof = {}          # the ncu counters were taken on another workload: no traffic / issue figure for this one
         value = rate["value"]
         sm_mhz = (clocks or {}).get("sm_mhz") or sm_max_mhz
         issue = None

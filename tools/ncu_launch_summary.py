@@ -101,7 +101,7 @@ def main():
              "warp_instructions_parts": {s: int(stage[s]["warp_instructions"]) for s in path_stages},
              "warp_instructions_source": f"ncu smsp__inst_executed.sum, one launch of each stage kernel (720p, N=10), averaged over the launch list {rel}",
              "source": f"ncu --clock-control none, dram__bytes_read.sum + dram__bytes_write.sum per launch of k1_search and k1_fuse<10> (720p, N=10), averaged over the launch list {rel}",
-             "algorithmic_bytes_per_launch": 98611200,
+             "algorithmic_bytes_per_launch": 98611200, "camera": "720p", "neighbours": 10,
              "commit": commit}
         with open(os.path.join(ROOT, "profiles", "k1_traffic.json"), "w") as f:
             json.dump(d, f, indent=1)
