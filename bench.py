@@ -63,7 +63,7 @@ def parse():
     ap.add_argument("--nkf", type=int, default=200, help="key frames per GPU")
     ap.add_argument("--nbr", type=int, default=10, help="covisible neighbours")
     ap.add_argument("--prior-sigmas", type=float, default=2.0, help="inverse-depth prior = mean +- s*sigma (PM.cc:381-382 uses 2)")
-    ap.add_argument("--cpu-sample", type=int, default=12, help="key frames in the CPU-baseline sample")
+    ap.add_argument("--cpu-sample", type=int, default=20, help="key frames in the CPU-baseline sample (SURVEY 8d: a 20-key-frame slice)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the short runs of BASELINE configs 1, 3, 5")
     ap.add_argument("--no-seam-check", action="store_true")
@@ -654,6 +654,19 @@ def run_b200(args):
         dt = cpu_pass(po, plan, images, threads)
         line["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
                                 "sample": f"first {sample} key frames of the same workload, all stages K0..K5, oracle port with OpenMP on the reference's five pragma loops (one pass, {dt:.1f} s)"}
+        # "as shipped": the reference builds without -fopenmp -> one thread, on the smallest sample that still
+        # has n neighbours per key frame; and BASELINE config 1 in full (the reference's own CPU-runnable case), both ways
+        s1 = n + 1
+        _, plan1, images1 = cpu_sample_plan(args, synth, po, s1)
+        dt1 = cpu_pass(po, plan1, images1, 1)
+        line["cpu_baseline_1thread"] = {"value": s1 / dt1, "unit": UNIT, "cores": 1, "kind": "port",
+                                        "sample": f"first {s1} key frames of the same workload, one pass ({dt1:.1f} s)"}
+        if "configs" in line and "config1_480p_n6" in line["configs"]:
+            a1 = argparse.Namespace(**dict(vars(args), camera="480p", nbr=6, prior_sigmas=2.0))
+            _, planc, imagesc = cpu_sample_plan(a1, synth, po, 10)
+            dtc, dtc1 = cpu_pass(po, planc, imagesc, threads), cpu_pass(po, planc, imagesc, 1)
+            line["configs"]["config1_480p_n6"]["cpu_baseline"] = {"value": 10 / dtc, "cores": threads, "value_1thread": 10 / dtc1,
+                                                                  "unit": UNIT, "kind": "port", "sample": "all 10 key frames, one pass each"}
     if rank == 0:
         emit(line)
     if world > 1:
