@@ -491,7 +491,7 @@ def run_b200(args):
         t_host = time.perf_counter()
         for _ in range(steps):
             work.step(leg)
-        host_issue_ms[leg] = 1e3 * (time.perf_counter() - t_host) / steps   # host time to ISSUE a step (no device wait)
+        host_issue_ms[leg] = 1e3 * (time.perf_counter() - t_host) / steps   # host time inside the issue loop: includes waiting on a full launch queue / download ring (tools/stage_costs.py measures the unblocked cost)
         ms = c.span_end()
         if leg in ("value", "e2e"):
             rank_clocks[leg] = nvml.stop()
