@@ -242,6 +242,28 @@ int sd_search_range(const float K1[4], const float Tcw1[12], const float Tcw2[12
 int sd_intra_depth_check_planes(sd_ctx* ctx, float* depth, float* sigma, const float* grad, int w, int h);
 int sd_intra_depth_grow_planes(sd_ctx* ctx, float* depth, float* sigma, const float* grad, int w, int h);
 
+/* sd_intra_depth_check_planes for callers that must not allocate device memory.  (No counterpart in the reference: it has
+ * no GPU code, so the question never arises there.)
+ * Who needs it: sd_intra_depth_check_planes obtains five working planes with cudaMalloc on every call and returns them
+ * with cudaFree.  Both go to the driver's allocator, take an unpredictable time, and cudaFree in addition waits for all
+ * work on the GPU -- including a key-frame pipeline this or another context has in flight.  A tracking or local-mapping
+ * thread with a frame deadline cannot afford that stall, and a process that handed all of its device memory to its own
+ * pool at start-up (or runs under a hard memory quota) may simply get cudaErrorMemoryAllocation.  This variant never calls
+ * cudaMalloc, cudaFree or any other allocating routine: the five working planes live in an array that is part of
+ * libsdpm.so's device image, 5 * SD_STATIC_MAX_PIXELS floats (17.6 MiB) on every GPU that loads the library, until the
+ * process exits.
+ * Same arguments, same arithmetic and the same results, bit for bit, as sd_intra_depth_check_planes; w * h above
+ * SD_STATIC_MAX_PIXELS is refused with SD_ERR_INVALID_ARG (sd_last_error names the limit).  Synchronous.
+ * First call on each GPU: the library looks up the array's device address (cudaGetSymbolAddress, with the context's
+ * device current) and remembers it; this makes the driver load the module, so make that first call during start-up,
+ * before any CUDA stream capture begins.
+ * Sharing: all calls on one GPU, from every context in the process, use the same array, and it keeps what the last call
+ * left in it.  Nothing in it has to be cleared between calls (each call overwrites the input planes and the kernel writes
+ * every output pixel), but two calls that are on the GPU at the same time overwrite each other's planes: the caller
+ * serialises them per GPU. */
+#define SD_STATIC_MAX_PIXELS (1280 * 720)
+int sd_intra_depth_check_planes_static(sd_ctx* ctx, float* depth, float* sigma, const float* grad, int w, int h);
+
 /* ---- single-pixel probes (run the same device code as the batch kernels; for unit tests) ---- */
 /* EpipolarSearch PM.cc:385-465 for n pixels xy[2*i], xy[2*i+1] of kf1 against kf2.
  * out[6*i..] = {inverse depth, sigma, best integer uj (or -1), supported, best_u (the refined u*, PM.cc:459),

@@ -17,6 +17,7 @@ LIB_PATH = os.path.join(_HERE, "lib", "libsdpm.so")
 INCLUDE_DIR = os.path.join(os.path.dirname(_HERE), "include")
 
 SD_MAX_NEIGHBOURS = 40
+SD_STATIC_MAX_PIXELS = 1280 * 720   # include/sdpm.h: largest plane sd_intra_depth_check_planes_static accepts
 GRAD, THETA, DEPTH, SIGMA, DEPTH_CHECKED, POINTS = range(6)
 
 STATUS = {0: "SD_OK", -1: "SD_ERR_INVALID_ARG", -2: "SD_ERR_UNKNOWN_KEYFRAME", -3: "SD_ERR_NOT_READY",
@@ -110,6 +111,7 @@ SYMBOLS = {
     "sd_search_range": (C.c_int, [_fp, _fp, _fp, C.c_int, C.c_int, C.c_int, C.c_float, C.c_float, _fp, _fp]),
     "sd_intra_depth_check_planes": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
     "sd_intra_depth_grow_planes": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
+    "sd_intra_depth_check_planes_static": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int]),
     "sd_probe_epipolar": (C.c_int, [_vp, C.c_int, C.c_int, _ip, C.c_int, C.c_float, C.c_float, C.c_float, _fp]),
     "sd_probe_fusion": (C.c_int, [_vp, _fp, _fp, C.c_int, _fp, _fp, _ip]),
 }
@@ -447,6 +449,16 @@ class Context:
         h, w = d.shape
         fn = self.L.sd_intra_depth_grow_planes if grow else self.L.sd_intra_depth_check_planes
         self._ck(fn(self.h, d.ctypes.data, s.ctypes.data, g.ctypes.data, w, h))
+        return d, s
+
+    def intra_check_planes_static(self, depth, sigma, grad):
+        """sd_intra_depth_check_planes_static: IntraKeyFrameDepthChecking on host planes without any device allocation
+        (working planes built into the library, at most STATIC_MAX_PIXELS pixels); returns new (depth, sigma)."""
+        d = np.array(depth, np.float32, order="C")
+        s = np.array(sigma, np.float32, order="C")
+        g = np.ascontiguousarray(grad, np.float32)
+        h, w = d.shape
+        self._ck(self.L.sd_intra_depth_check_planes_static(self.h, d.ctypes.data, s.ctypes.data, g.ctypes.data, w, h))
         return d, s
 
     def probe_epipolar(self, kf1, kf2, xy, min_depth, max_depth, rot):

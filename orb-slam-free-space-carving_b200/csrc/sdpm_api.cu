@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <unordered_map>
 #include <vector>
@@ -1548,6 +1549,74 @@ int sd_intra_depth_check_planes(sd_ctx* c, float* depth, float* sigma, const flo
 
 int sd_intra_depth_grow_planes(sd_ctx* c, float* depth, float* sigma, const float* grad, int w, int h) {
     return intra_planes(c, depth, sigma, grad, w, h, true);
+}
+
+// ---- the entry point that allocates nothing ----
+// Working planes of sd_intra_depth_check_planes_static: three uploaded inputs + two outputs, each up to
+// SD_STATIC_MAX_PIXELS floats.  The array belongs to the loaded module, one copy per GPU that loads libsdpm.so, held until
+// the process exits.  In host code `g_static_planes` is only a handle for cudaGetSymbolAddress: it is not a device address
+// and must never be handed to a kernel or a cudaMemcpy as one.
+static __device__ __align__(256) float g_static_planes[5 * (size_t)SD_STATIC_MAX_PIXELS];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+float* g_static_addr[kStaticMaxDevices] = {};  // device address of g_static_planes on each GPU, looked up once
+
+// The caller has made `device` current.
+int static_planes_addr(sd_ctx* c, int device, float** out) {
+    if (device < 0 || device >= kStaticMaxDevices) return fail(c, SD_ERR_INVALID_ARG, "sd_intra_depth_check_planes_static: device %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_addr[device]) {
+        void* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_planes);
+        if (e != cudaSuccess || !p)
+            return fail(c, SD_ERR_CUDA, "cudaGetSymbolAddress(g_static_planes) on device %d: %s", device, cudaGetErrorString(e));
+        g_static_addr[device] = static_cast<float*>(p);
+    }
+    *out = g_static_addr[device];
+    return SD_OK;
+}
+}  // namespace
+
+int sd_intra_depth_check_planes_static(sd_ctx* c, float* depth, float* sigma, const float* grad, int w, int h) {
+    if (!c || !depth || !sigma || !grad || w < 8 || h < 8)
+        return fail(c, SD_ERR_INVALID_ARG, "sd_intra_depth_check_planes_static: bad argument");
+    if ((long long)w * h > (long long)SD_STATIC_MAX_PIXELS)
+        return fail(c, SD_ERR_INVALID_ARG,
+                    "sd_intra_depth_check_planes_static: %d x %d = %lld pixels is more than SD_STATIC_MAX_PIXELS = %d, the size of the "
+                    "library's built-in working planes; use sd_intra_depth_check_planes for larger planes",
+                    w, h, (long long)w * h, (int)SD_STATIC_MAX_PIXELS);
+    CU(c, cudaSetDevice(c->device));
+    float* d = nullptr;
+    const int rc = static_planes_addr(c, c->device, &d);
+    if (rc != SD_OK) return rc;
+    const size_t npix = (size_t)w * h, bytes = npix * sizeof(float);
+    float *d_depth = d, *d_sigma = d + npix, *d_grad = d + 2 * npix, *o_depth = d + 3 * npix, *o_sigma = d + 4 * npix;
+    // Nothing here has to start at zero: the uploads overwrite the three input planes and the kernel stores every pixel
+    // of both output planes, so whatever the previous call left behind is never read.
+    cudaError_t e = cudaMemcpyAsync(d_depth, depth, bytes, cudaMemcpyHostToDevice, c->s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_sigma, sigma, bytes, cudaMemcpyHostToDevice, c->s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(d_grad, grad, bytes, cudaMemcpyHostToDevice, c->s_main);
+    if (e == cudaSuccess) {
+        IntraArgs S;
+        S.W = w; S.H = h; S.pitch_in = w; S.pitch_out = w; S.border = c->P.border;
+        S.vec_ok = (w % 4 == 0) && (npix % 4 == 0);  // the array is 256-byte aligned and the planes start npix floats apart
+        S.lambdaG = c->P.lambdaG; S.chi_fuse = c->chi_fuse_f; S.grad = d_grad;
+        S.depth_in = d_depth; S.sigma_in = d_sigma; S.depth_out = o_depth; S.sigma_out = o_sigma;
+        S.depth_copy = nullptr; S.vlist = nullptr; S.vcount = nullptr;
+        dim3 grd((w + K23_TW - 1) / K23_TW, (h + K23_TH - 1) / K23_TH);
+        k23_intra<true, false><<<grd, K23_THREADS, K23_SMEM, c->s_main>>>(S);
+        c->launches++;
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(depth, o_depth, bytes, cudaMemcpyDeviceToHost, c->s_main);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sigma, o_sigma, bytes, cudaMemcpyDeviceToHost, c->s_main);
+    // wait in every case: the caller's planes must not be the target or source of a copy still in flight on return
+    const cudaError_t es = cudaStreamSynchronize(c->s_main);
+    if (e == cudaSuccess) e = es;
+    if (e != cudaSuccess) return fail(c, SD_ERR_CUDA, "sd_intra_depth_check_planes_static: %s", cudaGetErrorString(e));
+    return SD_OK;
 }
 
 // ---- probes ----
