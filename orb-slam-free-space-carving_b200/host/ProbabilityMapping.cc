@@ -80,13 +80,15 @@ bool ProbabilityMapping::isFinished() {
 // The reference reads GetRotation()/GetTranslation() at call time (PM.cc:638-644, 854-860, 973-979):
 // the pose the device holds is refreshed whenever the view's has moved.
 ProbabilityMapping::KfState& ProbabilityMapping::make_resident(KeyFrameView* kf) {
+    float Tcw[12];
+    kf->GetPose(Tcw);  // one copy under mMutexPose: SetPose on another thread cannot hand a torn pose to the device
     auto it = resident_.find(kf->mnId);
     if (it == resident_.end()) {
         if (kf->im_.empty()) throw std::invalid_argument("ProbabilityMapping: key frame without image");
-        check(sd_upload_keyframe(ctx_, kf->mnId, kf->im_.data, kf->im_.cols, kf->im_.rows, kf->im_.stride, kf->K, kf->Tcw),
+        check(sd_upload_keyframe(ctx_, kf->mnId, kf->im_.data, kf->im_.cols, kf->im_.rows, kf->im_.stride, kf->K, Tcw),
               "sd_upload_keyframe");
         KfState st;
-        std::memcpy(st.Tcw, kf->Tcw, sizeof(st.Tcw));
+        std::memcpy(st.Tcw, Tcw, sizeof(st.Tcw));
         it = resident_.emplace(kf->mnId, st).first;
         const size_t px = (size_t)kf->im_.rows * kf->im_.cols;
         if (kf->semidense_flag_ && kf->depth_map_.size() == px && kf->depth_sigma_.size() == px) {
@@ -95,9 +97,9 @@ ProbabilityMapping::KfState& ProbabilityMapping::make_resident(KeyFrameView* kf)
             check(sd_import_maps_host(ctx_, kf->mnId, kf->depth_map_.data(), kf->depth_sigma_.data()), "sd_import_maps_host");
             it->second.imported = true;
         }
-    } else if (std::memcmp(it->second.Tcw, kf->Tcw, sizeof(it->second.Tcw)) != 0) {
-        check(sd_set_pose(ctx_, kf->mnId, kf->Tcw), "sd_set_pose");
-        std::memcpy(it->second.Tcw, kf->Tcw, sizeof(it->second.Tcw));
+    } else if (std::memcmp(it->second.Tcw, Tcw, sizeof(it->second.Tcw)) != 0) {
+        check(sd_set_pose(ctx_, kf->mnId, Tcw), "sd_set_pose");
+        std::memcpy(it->second.Tcw, Tcw, sizeof(it->second.Tcw));
     }
     return it->second;
 }
@@ -167,13 +169,13 @@ void ProbabilityMapping::SemiDenseLoop() {
         if (num_depth_kf < covis_n_) continue;
         // InterKeyFrameDepthChecking + UpdateSemiDensePointSet (PM.cc:302-304): one fused launch
         std::vector<int> ids;
+        kf->poseChanged = false;  // cleared BEFORE the pose is read: a SetPose that lands later raises it again (next pass)
         make_resident(kf);
         for (KeyFrameView* n : neighbors) {
             make_resident(n);
             ids.push_back(n->mnId);
         }
         check(sd_interkf_check_points(ctx_, kf->mnId, ids.data(), (int)ids.size()), "sd_interkf_check_points");
-        kf->poseChanged = false;
         kf->interKF_depth_flag_ = true;
         if (std::find(changed_.begin(), changed_.end(), kf) == changed_.end()) changed_.push_back(kf);
     }
@@ -214,8 +216,10 @@ void ProbabilityMapping::StereoSearchConstraints(KeyFrameView* kf, float* min_de
 }
 
 void ProbabilityMapping::ComputeFundamental(KeyFrameView* pKF1, KeyFrameView* pKF2, float F12[9]) {
-    float R21[9], t21[3];
-    check(sd_pair_geometry(pKF1->K, pKF1->Tcw, pKF2->K, pKF2->Tcw, F12, R21, t21), "sd_pair_geometry");
+    float R21[9], t21[3], T1[12], T2[12];
+    pKF1->GetPose(T1);
+    pKF2->GetPose(T2);
+    check(sd_pair_geometry(pKF1->K, T1, pKF2->K, T2, F12, R21, t21), "sd_pair_geometry");
 }
 
 float ProbabilityMapping::MedianRotInPlane(KeyFrameView* kf1, KeyFrameView* kf2) {
@@ -249,7 +253,10 @@ void ProbabilityMapping::EpipolarSearch(KeyFrameView* kf1, KeyFrameView* kf2, co
 void ProbabilityMapping::GetSearchRange(float& umin, float& umax, int px, int py, float mind, float maxd, KeyFrameView* kf,
                                         KeyFrameView* kf2) {
     const int cols = kf->im_.cols;
-    check(sd_search_range(kf->K, kf->Tcw, kf2->Tcw, cols, px, py, mind, maxd, &umin, &umax), "sd_search_range");
+    float T1[12], T2[12];
+    kf->GetPose(T1);
+    kf2->GetPose(T2);
+    check(sd_search_range(kf->K, T1, T2, cols, px, py, mind, maxd, &umin, &umax), "sd_search_range");
 }
 
 void ProbabilityMapping::InverseDepthHypothesisFusion(const std::vector<depthHo>& h, depthHo& dist) {
@@ -298,9 +305,9 @@ void ProbabilityMapping::InterKeyFrameDepthChecking(KeyFrameView* currentKf, std
 }
 
 void ProbabilityMapping::UpdateSemiDensePointSet(KeyFrameView* kf) {
+    kf->poseChanged = false;  // PM.cc:331; before the pose is read, so that a concurrent SetPose is not lost
     make_resident(kf);  // uploads / re-installs if needed and pushes the current pose (PM.cc:340: GetPoseInverse at call time)
     check(sd_update_pointset(ctx_, kf->mnId), "sd_update_pointset");
-    kf->poseChanged = false;  // PM.cc:331
 }
 
 void ProbabilityMapping::UpdateAllSemiDensePointSet() {
@@ -375,8 +382,8 @@ void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
 }
 
 int ProbabilityMapping::ConfidentPoints(KeyFrameView* kf, std::vector<Point3f>& out, double max_sigma, int max_points) {
-    make_resident(kf);  // PM.cc:329-331: points follow the current pose
     kf->poseChanged = false;
+    make_resident(kf);  // PM.cc:329-331: points follow the current pose
     static_assert(sizeof(Point3f) == 3 * sizeof(float), "Point3f must be three packed floats");
     // the selection stays on the device; its size decides the host buffer, then one copy
     const float *dx = nullptr, *ds = nullptr;

@@ -18,7 +18,8 @@
 //
 // Threading: Run() is the reference's polling worker (PM.cc:65-134; the pattern of
 // Modeler::Run, Modeler.cc:51-98, started like System.cc:110-111) and is meant to own the object
-// from its own thread; RequestFinish() / isFinished() and Map::AddKeyFrame() are the only calls
+// from its own thread; RequestFinish() / isFinished(), Map::AddKeyFrame() and KeyFrameView::SetPose() (bundle adjustment,
+// loop closing; the pose is read under the key frame's mMutexPose, one consistent copy per use) are the only calls
 // another thread may make while it runs.
 #ifndef SDPM_HOST_PROBABILITYMAPPING_H
 #define SDPM_HOST_PROBABILITYMAPPING_H
@@ -62,7 +63,10 @@ struct KeyFrameView {
     int mnId = -1;
     PlaneView<const uint8_t> im_;  // kf->im_ / GetImage(), PM.cc:186
     float K[4] = {0, 0, 0, 0};     // fx, fy, cx, cy  (kf->fx ..., PM.cc:862-865; GetCalibrationMatrix, PM.cc:675)
-    float Tcw[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};  // GetRotation / GetTranslation, PM.cc:885-888
+    // GetRotation / GetTranslation, PM.cc:885-888.  Guarded by mMutexPose like KeyFrame::Tcw (KeyFrame.cc:70-119): once
+    // the worker runs, write it through SetPose and read it through GetPose only.
+    float Tcw[12] = {1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0};
+    mutable std::mutex mMutexPose;
     std::atomic<bool> bad{false};     // isBad(); other SLAM threads flip these while the worker runs
     std::atomic<bool> mapped{true};   // Mapped(), PM.cc:156
     std::vector<KeyFrameView*> covisible;  // GetVectorCovisibleKeyFrames(), best first, PM.cc:151
@@ -76,9 +80,16 @@ struct KeyFrameView {
 
     bool isBad() const { return bad.load(); }
     bool Mapped() const { return mapped.load(); }
-    void SetPose(const float Tcw_new[12]) {  // KeyFrame::SetPose + poseChanged (PM.cc:329)
-        for (int i = 0; i < 12; ++i) Tcw[i] = Tcw_new[i];
+    void SetPose(const float Tcw_new[12]) {  // KeyFrame::SetPose (KeyFrame.cc:70-84) + poseChanged (PM.cc:329)
+        {
+            std::unique_lock<std::mutex> lock(mMutexPose);
+            for (int i = 0; i < 12; ++i) Tcw[i] = Tcw_new[i];
+        }
         poseChanged = true;
+    }
+    void GetPose(float out[12]) const {  // GetRotation + GetTranslation as one consistent copy (KeyFrame.cc:109-119)
+        std::unique_lock<std::mutex> lock(mMutexPose);
+        for (int i = 0; i < 12; ++i) out[i] = Tcw[i];
     }
 };
 

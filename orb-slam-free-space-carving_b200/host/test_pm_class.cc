@@ -127,11 +127,33 @@ int main(int argc, char** argv) {
             pm.SetResidentLimit((size_t)limit);
             pm.SetPointCloudPath(argc >= 4 ? argv[3] : "");
             std::thread worker([&pm] { pm.Run(); });  // started like mptModeler, System.cc:110-111
+            // a third thread plays bundle adjustment / loop closing: it keeps announcing poses (the true ones, so the
+            // expected result does not change) through SetPose while the worker reads them under mMutexPose
+            std::atomic<int> inserted{0};
+            std::atomic<bool> stop_poses{false};
+            std::atomic<uint64_t> pose_writes{0};
+            std::thread poses([&] {
+                std::vector<float> T(12);
+                for (uint64_t k = 0; !stop_poses.load(); ++k) {
+                    const int n = inserted.load();
+                    if (n > 0) {
+                        KeyFrameView* kf = kfs[(size_t)((k * 7919u) % (uint64_t)n)].get();
+                        kf->GetPose(T.data());
+                        kf->SetPose(T.data());
+                        pose_writes++;
+                    }
+                    usleep(1500);
+                }
+            });
             for (int i = 0; i < nkf; ++i) {
                 kfs[i]->mapped = true;
                 map.AddKeyFrame(kfs[i].get());
+                inserted = i + 1;
                 usleep(i % 3 == 0 ? 20000 : 1000);     // irregular arrival, several worker passes in between
             }
+            stop_poses = true;
+            poses.join();
+            std::printf("stream: %llu SetPose calls from a second thread while the worker ran\n", (unsigned long long)pose_writes.load());
             const uint64_t p0 = pm.Passes();
             while (pm.Passes() < p0 + 2) usleep(1000);  // two full passes after the last insertion
             pm.RequestFinish();
