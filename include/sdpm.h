@@ -113,7 +113,11 @@ int sd_interkf_check_points(sd_ctx* ctx, int kf_id, const int* nbr_ids, int n);
  * issued by one call: sd_semidense for every item in order, and -- with SD_LOOP_INTERKF -- sd_interkf_check_points of an
  * item as soon as the maps of all its neighbours have been queued (neighbours outside the list must already have maps;
  * an item whose neighbours lack them is skipped like PM.cc:289-297 and reported in inter_done).  Downloads (dense or
- * compact, see below) of an item's results are queued right after its last stage when the item asks for them. */
+ * compact, see below) of an item's results are queued right after its last stage when the item asks for them.
+ * A skipped item has no point set: its SD_DL_DENSE / SD_DL_COMPACT download still delivers the intra-key-frame maps,
+ * SD_DL_COMPACT_POINTS sets *out_count = 0, SD_DL_DENSE_POINTS leaves the buffers untouched -- pass inter_done to tell.
+ * With SdParams.interkf_inplace the checks are order-dependent, so they are issued strictly in list order after all the
+ * searches (PM.cc:262's loop order) instead of as early as possible. */
 enum { SD_LOOP_INTERKF = 1 };
 enum { SD_DL_NONE = 0, SD_DL_DENSE = 1, SD_DL_DENSE_POINTS = 2, SD_DL_COMPACT = 3, SD_DL_COMPACT_POINTS = 4 };
 typedef struct SdLoopItem {

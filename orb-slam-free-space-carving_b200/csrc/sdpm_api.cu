@@ -84,6 +84,7 @@ struct sd_ctx {
     // k1_fuse output / k23_intra input, one pair per hypothesis buffer; invariant: all zero while no key frame is in
     // flight on the buffer (k23_intra is followed by the memsets that restore it, off the key frame's own dependency chain)
     float *tmp_depth[2] = {nullptr, nullptr}, *tmp_sigma[2] = {nullptr, nullptr};
+    bool tmp_dirty[2] = {false, false};  // a fusion was queued into the pair and the restoring memset has not been (error path)
     float2* hyp[2] = {nullptr, nullptr};               // hypothesis buffers of k1_search, [neighbour][hyp_stride], double-buffered
     int hyp_stride = 0, hyp_rows = 0, hyp_turn = 0;
     cudaEvent_t ev_srch[2] = {nullptr, nullptr};       // k1_search into hyp[b] done (s_srch)
@@ -281,7 +282,9 @@ int upload_common(sd_ctx* c, int kf_id, const uint8_t* gray, bool on_device, int
         for (int b = 0; b < 2; ++b) {
             CU(c, cudaMalloc(&c->tmp_depth[b], 2 * fplane));  // depth | sigma: one memset restores both
             c->tmp_sigma[b] = c->tmp_depth[b] + (size_t)c->pitch_f * c->H;
-            CU(c, cudaMemset(c->tmp_depth[b], 0, 2 * fplane));
+            // zeroed on the stream that uses them (k1_fuse runs on s_main): the streams are non-blocking, so a memset on the
+            // legacy default stream would have no formal ordering before the first fusion
+            CU(c, cudaMemsetAsync(c->tmp_depth[b], 0, 2 * fplane, c->s_main));
         }
     } else if (c->W != w || c->H != h) {
         return fail(c, SD_ERR_SHAPE, "key frame %d is %dx%d, context is %dx%d", kf_id, w, h, c->W, c->H);
@@ -635,6 +638,9 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     }
     CU(c, wait_map_readers(c, s));  // k23_intra below overwrites this key frame's maps and list (k1_fuse zeroes meta->valid_count)
     const size_t fplane = (size_t)c->pitch_f * c->H * sizeof(float);
+    if (c->tmp_dirty[hb])  // an earlier call failed between its fusion and the memset that restores the planes
+        CU(c, cudaMemsetAsync(c->tmp_depth[hb], 0, 2 * fplane, c->s_main));
+    c->tmp_dirty[hb] = true;
     {
         ScopedTimer t(c, c->s_main, T_FUSE);
         FuseArgs F;
@@ -666,6 +672,7 @@ int sd_semidense(sd_ctx* c, int kf_id, const int* nbr_ids, const float* nbr_rot_
     // the scratch planes (one allocation per buffer: depth | sigma) go back to all-zero for the next key frame that uses
     // buffers [hb] -- after the maps-ready record, so not on this key frame's dependency chain
     CU(c, cudaMemsetAsync(c->tmp_depth[hb], 0, 2 * fplane, c->s_main));
+    c->tmp_dirty[hb] = false;
     CU(c, cudaEventRecord(c->ev_hypfree[hb], c->s_main));
     c->hypfree_valid[hb] = true;
     s->has_semidense = true;
@@ -1058,6 +1065,7 @@ int sd_import_maps(sd_ctx* c, int kf_id, const float* depth_dev, const float* si
     record_maps(c, s);
     s->has_semidense = true;
     s->has_checked = false;
+    s->has_points = false;  // the point set on the device belongs to the maps just replaced
     s->vlist_ok = false;
     return SD_OK;
 }
@@ -1112,9 +1120,8 @@ struct NcclApi {
 
 NcclApi* nccl_api() {
     static NcclApi api;
-    static bool tried = false;
-    if (!tried) {
-        tried = true;
+    static std::once_flag once;  // contexts may be created from several threads: one dlopen, finished before anyone reads `api`
+    std::call_once(once, [] {
         // a process that already loaded NCCL (torch ships its own libnccl.so.2) gets that copy back
         const char* names[] = {getenv("SDPM_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
         for (const char* nm : names) {
@@ -1135,7 +1142,7 @@ NcclApi* nccl_api() {
                 !api.recv)
                 api.lib = nullptr;
         }
-    }
+    });
     return api.lib ? &api : nullptr;
 }
 
@@ -1216,20 +1223,28 @@ int sd_halo_exchange(sd_ctx* c, const SdHaloPeer* peers, int n_peers) {
         }
     }
     NC(c, api, api->group_start());
-    for (int p = 0; p < n_peers; ++p) {
+    // an error inside the bracket must not return with the group still open on this thread (the peers would block in
+    // their grouped receives): stop queueing, close the group, then report the first error
+    int nerr = 0;
+    const char* nwhat = "";
+    for (int p = 0; p < n_peers && !nerr; ++p) {
         const SdHaloPeer& P = peers[p];
-        for (int i = 0; i < P.n_send; ++i) {
+        for (int i = 0; i < P.n_send && !nerr; ++i) {
             Slot* s = find(c, P.send_ids[i]);
-            NC(c, api, api->send(s->depth, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
-            NC(c, api, api->send(s->sigma, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
+            nerr = api->send(s->depth, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main);
+            if (!nerr) nerr = api->send(s->sigma, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main);
+            if (nerr) nwhat = "ncclSend";
         }
-        for (int i = 0; i < P.n_recv; ++i) {
+        for (int i = 0; i < P.n_recv && !nerr; ++i) {
             Slot* s = find(c, P.recv_ids[i]);
-            NC(c, api, api->recv(s->depth, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
-            NC(c, api, api->recv(s->sigma, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main));
+            nerr = api->recv(s->depth, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main);
+            if (!nerr) nerr = api->recv(s->sigma, plane, kNcclFloat32, P.peer, c->nccl_comm, c->s_main);
+            if (nerr) nwhat = "ncclRecv";
         }
     }
-    NC(c, api, api->group_end());
+    const int gerr = api->group_end();
+    if (nerr) return fail(c, SD_ERR_CUDA, "sd_halo_exchange: %s: NCCL error %d (%s)", nwhat, nerr, api->err ? api->err(nerr) : "?");
+    if (gerr) return fail(c, SD_ERR_CUDA, "sd_halo_exchange: ncclGroupEnd: NCCL error %d (%s)", gerr, api->err ? api->err(gerr) : "?");
     for (int p = 0; p < n_peers; ++p) {
         const SdHaloPeer& P = peers[p];
         for (int i = 0; i < P.n_recv; ++i) {
@@ -1290,11 +1305,15 @@ int sd_semidense_loop(sd_ctx* c, const SdLoopItem* items, int n_items, int flags
     // items in list order; the finishing stages of item j are queued right after the sd_semidense of the last item it
     // waits for (so downloads and checks overlap the remaining searches); a pending pointer walks the list in order,
     // like PM.cc:262's loop
+    // In-place mode (SdParams.interkf_inplace) makes the checks order-dependent: there they are issued strictly in list
+    // order once every search has been queued, which is the order of PM.cc:262's loop over vpKFs.
+    const bool in_order = (flags & SD_LOOP_INTERKF) && c->P.interkf_inplace != 0;
     std::vector<std::vector<int>> due(n_items);
-    std::vector<int> skipped;
+    std::vector<int> skipped, ordered;
     for (int i = 0; i < n_items; ++i) {
-        if (ready_at[i] >= 0) due[ready_at[i]].push_back(i);
-        else skipped.push_back(i);
+        if (ready_at[i] < 0) skipped.push_back(i);
+        else if (in_order) ordered.push_back(i);
+        else due[ready_at[i]].push_back(i);
     }
     for (int k = 0; k < n_items; ++k) {
         const SdLoopItem& it = items[k];
@@ -1308,8 +1327,16 @@ int sd_semidense_loop(sd_ctx* c, const SdLoopItem* items, int n_items, int flags
             if (rc != SD_OK) return rc;
         }
     }
+    for (int i : ordered) {
+        int rc = finish(i);
+        if (rc != SD_OK) return rc;
+    }
     for (int i : skipped) {  // no inter-key-frame stage in this pass; a requested download still delivers the intra maps
-        if (items[i].download == SD_DL_NONE || items[i].download == SD_DL_DENSE_POINTS || items[i].download == SD_DL_COMPACT_POINTS) continue;
+        if (items[i].download == SD_DL_NONE || items[i].download == SD_DL_DENSE_POINTS) continue;
+        if (items[i].download == SD_DL_COMPACT_POINTS) {  // no point set exists: say so instead of leaving a stale count behind
+            if (items[i].out_count) *items[i].out_count = 0;
+            continue;
+        }
         int rc = finish(i);
         if (rc != SD_OK) return rc;
     }

@@ -174,7 +174,27 @@ def test_semidense_loop_dense_downloads_and_skips(pkg, po, synth, pipeline):
         assert np.array_equal(ctx2.plane(k, po.DEPTH), ora.plane(k, po.DEPTH))
         if e:
             assert np.array_equal(ctx2.plane(k, po.DEPTH_CHECKED), ora.plane(k, po.DEPTH_CHECKED))
-    ctx.close(); ctx2.close()
+    # a skipped item that asked for compact records WITH points has no point set: its count comes back 0, not stale
+    ctx3 = pkg.Context(0)
+    pipeline.upload_all(ctx3, plan, images)
+    cap = (scene.w - 4) * (scene.h - 4)
+    recs = torch.zeros((5, cap * pkg.COMPACT_POINT.itemsize), dtype=torch.uint8).pin_memory()
+    counts = torch.full((5,), 12345, dtype=torch.int32).pin_memory()
+    half = [dict(kf_id=k, nbrs=plan.nbrs[k], rots=plan.rots[k], prior=plan.prior[k],
+                 download=(pkg.SD_DL_COMPACT_POINTS, recs[i].data_ptr(), cap, counts[i:].data_ptr()))
+            for i, k in enumerate(plan.ids[:5])]
+    done = ctx3.semidense_loop(ctx3.make_loop(half))
+    ctx3.sync()
+    assert list(done.astype(bool)) == expect
+    for i, (k, e) in enumerate(zip(plan.ids[:5], expect)):
+        if not e:
+            assert int(counts[i]) == 0
+        else:
+            m = int(counts[i])
+            assert 0 < m <= cap
+            d, _, p = pkg.expand_compact(recs[i].numpy().view(pkg.COMPACT_POINT)[:m], scene.h, scene.w, points=True)
+            assert np.array_equal(d, ora.plane(k, po.DEPTH_CHECKED)) and np.array_equal(p, ora.plane(k, po.POINTS))
+    ctx.close(); ctx2.close(); ctx3.close()
 
 
 def test_interkf_inplace_mode(pkg, po, synth, pipeline):
@@ -200,7 +220,17 @@ def test_interkf_inplace_mode(pkg, po, synth, pipeline):
     ctx2.sync()
     for k in plan.ids:
         assert np.array_equal(ctx2.plane(k, po.DEPTH_CHECKED), ora.plane(k, po.DEPTH_CHECKED))
-    ctx.close(); ctx2.close()
+    # and so does sd_semidense_loop: in this mode it issues the checks in list order after all the searches (PM.cc:262's
+    # order), not as soon as an item's neighbours are queued
+    ctx3 = pkg.Context(0, gp)
+    pipeline.upload_all(ctx3, plan, images)
+    items = [dict(kf_id=k, nbrs=plan.nbrs[k], rots=plan.rots[k], prior=plan.prior[k]) for k in plan.ids]
+    assert ctx3.semidense_loop(ctx3.make_loop(items)).all()
+    ctx3.sync()
+    for k in plan.ids:
+        for which in (po.DEPTH_CHECKED, po.POINTS):
+            assert np.array_equal(ctx3.plane(k, which), ora.plane(k, which)), (k, which)
+    ctx.close(); ctx2.close(); ctx3.close()
 
 
 def test_reupload_then_import_with_work_queued(pkg, po, synth, pipeline):
