@@ -4,8 +4,9 @@ K0..K3 of a key frame read only IMAGE planes of its neighbours; K4 (InterKeyFram
 PM.cc:628-799) reads the neighbours' post-intra (inverse depth, sigma) maps.  So the sequence is
 cut into contiguous index ranges, one per rank (one process per GPU), and there is exactly one
 exchange step: after K3 every rank sends the maps of the boundary key frames its neighbours need
-and receives the ones it needs, as point-to-point torch.distributed ops (NCCL over NVLink on the
-GPUs, gloo in the CPU tests).  Halo key frames' images are uploaded (and K0 run) redundantly on the
+and receives the ones it needs.  On the GPUs that step is sd_halo_exchange behind the C ABI (grouped
+ncclSend / ncclRecv straight out of / into the key-frame planes, include/sdpm.h); the CPU tests run
+the same plan with gloo point-to-point ops and host buffers (exchange_maps below).  Halo key frames' images are uploaded (and K0 run) redundantly on the
 ranks that need them: recomputing 9 B/px is cheaper than shipping 8 B/px of planes.
 
 Everything here is a pure function of (global key-frame count, world size, neighbour lists), so
