@@ -67,6 +67,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-configs", action="store_true", help="skip the short runs of BASELINE configs 1, 3, 5")
     ap.add_argument("--no-seam-check", action="store_true")
+    ap.add_argument("--no-class-leg", action="store_true", help="skip e2e_class (the C++ drop-in class driven by lib/test_pm_class --bench)")
+    ap.add_argument("--class-window", type=int, default=16, help="key frames per sd_semidense_loop call of ProbabilityMapping::SemiDenseLoop")
     ap.add_argument("--seed", type=int, default=1234)
     return ap.parse_args()
 
@@ -642,8 +644,15 @@ def run_b200(args):
         }
         if seam is not None:
             line["seam_parity"] = seam
+    class_scene = None
+    if rank == 0 and world == 1 and not args.no_class_leg:
+        import tempfile
+        class_scene = os.path.join(tempfile.mkdtemp(prefix="sdpm_class_"), "scene.bin")
+        write_class_scene(class_scene, synth, wl, n)
     wl = None
     ctx.close()
+    if class_scene:
+        line["e2e_class"] = class_leg(args, class_scene, args.nkf)
     if rank == 0 and world == 1 and not args.no_configs:
         line["configs"] = other_configs(args, torch, pkg, synth, sharding, dev)
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -710,6 +719,62 @@ def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank):
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return {"keyframes_checked": int(t[0].item()), "planes": 3, "mismatching": int(t[1].item()),
             "checker": "CPU oracle on the +-N window around every seam, bitwise", "ranks": world}
+
+
+def write_class_scene(path, synth, wl, n):
+    """The bench workload as a scene file of host/test_pm_class.cc (format in its header): same images, poses, neighbour
+    lists and sparse depths as the C-ABI legs; key points such that GetRotInPlane's median is the trajectory's roll."""
+    import struct
+    scene, ids = wl.scene, list(wl.owned)
+    index = {k: i for i, k in enumerate(ids)}
+    hnp = wl.host_img.numpy()
+    with open(path, "wb") as f:
+        f.write(struct.pack("<4i", len(ids), scene.w, scene.h, n))
+        for k in ids:
+            f.write(struct.pack("<i", k))
+            f.write(np.asarray(scene.K, np.float32).tobytes())
+            f.write(np.asarray(wl.poses[k], np.float32).tobytes())
+            cov = [index[int(j)] for j in wl.plan.nbrs[k]]
+            f.write(struct.pack("<i", len(cov)))
+            f.write(np.asarray(cov, np.int32).tobytes())
+            d = np.asarray(scene.sparse_depths(k, 1000), np.float32)
+            f.write(struct.pack("<i", len(d)))
+            f.write(d.tobytes())
+            mp = np.arange(50, dtype=np.int64)
+            ang = np.full(50, 100.0, np.float32) + np.float32(synth.Scene.rot_in_plane(0, k))
+            f.write(struct.pack("<i", len(mp)))
+            f.write(mp.tobytes())
+            f.write(ang.tobytes())
+            f.write(hnp[wl.slot[k]].tobytes())
+        f.write(struct.pack("<i", 0))
+
+
+def class_leg(args, scene_path, nkf):
+    """e2e_class: the same workload through the drop-in C++ class (host/ProbabilityMapping.cc), timed by its own driver
+    with the host clock around whole passes: upload of every image, SemiDenseLoop in windows over sd_semidense_loop,
+    compact records with points downloaded asynchronously and EXPANDED into the dense depth_map_ / depth_sigma_ /
+    SemiDensePointSets_ members of every key frame (what PM.cc:225-226, 361-363 leave on the host)."""
+    import subprocess
+    import tempfile
+    driver = os.path.join(ROOT, "orb-slam-free-space-carving_b200", "lib", "test_pm_class")
+    out_path = os.path.join(os.path.dirname(scene_path), "class_out.bin")
+    steps = max(2, min(args.steps, 5))
+    try:
+        r = subprocess.run([driver, f"--bench={steps},2,{args.class_window},0", scene_path, out_path], capture_output=True, text=True, timeout=600)
+        got = [ln for ln in r.stdout.splitlines() if ln.startswith("bench: ")]
+        if r.returncode != 0 or not got:
+            return {"unavailable": (r.stderr or r.stdout).strip()[-300:]}
+        b = json.loads(got[0][len("bench: "):])
+        sys.stderr.write("".join(ln + "\n" for ln in r.stdout.splitlines() if ln.startswith("last pass")))
+    finally:
+        for q in (scene_path, out_path):
+            if os.path.exists(q):
+                os.remove(q)
+    return {"value": b["kf_per_s"], "unit": UNIT, "ms_per_step": b["ms_per_step"], "steps": b["steps"], "warmup": b["warmup"],
+            "window": b["window"], "inter_checked": b["inter_checked"], "keyframes": nkf, "clock": "host steady_clock around whole passes",
+            "what": "ProbabilityMapping::SemiDenseLoop (C++ drop-in class over the C ABI): image upload, windows of sd_semidense_loop, "
+                    "asynchronous compact downloads with points, records expanded into the dense KeyFrame members of EVERY key frame "
+                    "by host threads while the GPU runs the next window"}
 
 
 def other_configs(args, torch, pkg, synth, sharding, dev):

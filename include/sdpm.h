@@ -206,6 +206,12 @@ typedef struct SdHaloPeer {
 } SdHaloPeer;
 int sd_halo_exchange(sd_ctx* ctx, const SdHaloPeer* peers, int n_peers);
 
+/* Page-locked host memory for the asynchronous downloads above (SdLoopItem::out_records, sd_download_*_async): what a
+ * host without its own CUDA runtime calls uses -- host/ProbabilityMapping.cc sees the GPU through this header only.  (No
+ * reference counterpart.)  Allocate at start-up and reuse: like any page-locking call these are slow. */
+int sd_alloc_host(sd_ctx* ctx, uint64_t bytes, void** out);
+int sd_free_host(sd_ctx* ctx, void* ptr);
+
 int sd_sync(sd_ctx* ctx);
 const char* sd_last_error(sd_ctx* ctx);
 /* cudaStream_t of the compute stream, for callers that order their own device work after it */

@@ -1356,6 +1356,21 @@ int sd_export_maps(sd_ctx* c, int kf_id, float* depth_dev, float* sigma_dev) {
     return SD_OK;
 }
 
+int sd_alloc_host(sd_ctx* c, uint64_t bytes, void** out) {
+    if (!c || !out || bytes == 0) return fail(c, SD_ERR_INVALID_ARG, "sd_alloc_host: bad argument");
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaHostAlloc(out, (size_t)bytes, cudaHostAllocDefault));
+    return SD_OK;
+}
+
+int sd_free_host(sd_ctx* c, void* ptr) {
+    if (!c) return SD_ERR_INVALID_ARG;
+    if (!ptr) return SD_OK;
+    CU(c, cudaSetDevice(c->device));
+    CU(c, cudaFreeHost(ptr));
+    return SD_OK;
+}
+
 int sd_sync(sd_ctx* c) {
     if (!c) return SD_ERR_INVALID_ARG;
     CU(c, cudaSetDevice(c->device));

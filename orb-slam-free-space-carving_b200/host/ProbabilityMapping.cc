@@ -4,11 +4,18 @@
 #include "ProbabilityMapping.h"
 
 #include <unistd.h>
+#if defined(__SSE2__)
+#include <emmintrin.h>
+#endif
 
 #include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
+#include <new>
 #include <stdexcept>
+#include <thread>
 #include <unordered_set>
 
 namespace sdpm_host {
@@ -18,10 +25,18 @@ ProbabilityMapping::ProbabilityMapping(Map* pMap, int device, int covis_n, const
     if (covis_n < 1 || covis_n > SD_MAX_NEIGHBOURS) throw std::invalid_argument("ProbabilityMapping: covis_n out of range");
     int rc = sd_create(device, params, &ctx_);
     if (rc != SD_OK) throw std::runtime_error("ProbabilityMapping: sd_create failed (no usable CUDA device; there is no CPU fallback)");
+    inplace_ = params && params->interkf_inplace != 0;
 }
 
 ProbabilityMapping::~ProbabilityMapping() {
-    if (ctx_) sd_destroy(ctx_);
+    if (expander_.joinable()) expander_.join();
+    if (!ctx_) return;
+    sd_sync(ctx_);
+    for (BufferSet& b : bufs_) {
+        sd_free_host(ctx_, b.base);
+        sd_free_host(ctx_, b.counts);
+    }
+    sd_destroy(ctx_);
 }
 
 void ProbabilityMapping::check(int rc, const char* what) const {
@@ -147,46 +162,328 @@ std::vector<KeyFrameView*> ProbabilityMapping::pick_neighbours(KeyFrameView* kf)
     return closestMatches;
 }
 
+void ProbabilityMapping::ensure_buffers(BufferSet& b, size_t slots, int record_cap) {
+    if (b.base && b.slots >= slots && b.record_cap == record_cap) return;
+    check(sd_sync(ctx_), "sd_sync");
+    check(sd_free_host(ctx_, b.base), "sd_free_host");
+    check(sd_free_host(ctx_, b.counts), "sd_free_host");
+    b.base = nullptr; b.counts = nullptr;
+    void* p = nullptr;
+    check(sd_alloc_host(ctx_, (uint64_t)slots * record_cap * sizeof(SdCompactPoint), &p), "sd_alloc_host");
+    b.base = p;
+    check(sd_alloc_host(ctx_, (uint64_t)slots * sizeof(int), &p), "sd_alloc_host");
+    b.counts = static_cast<int*>(p);
+    b.slots = slots;
+    b.record_cap = record_cap;
+}
+
+// The pass of PM.cc:137-318, issued in windows (SetBatchWindow): per window ONE sd_semidense_loop call carries the
+// per-key-frame half of every key frame of the window (PM.cc:137-257), the inter-key-frame check + point set
+// (PM.cc:262-307) of every key frame -- of this or an earlier window or pass -- whose neighbours all have maps by then, and
+// the asynchronous download of what each of them produced.  The records of window k are expanded into the KeyFrame
+// members while the GPU works on window k+1.
 void ProbabilityMapping::SemiDenseLoop() {
+    using clk = std::chrono::steady_clock;
+    auto since = [](clk::time_point t) { return std::chrono::duration<double>(clk::now() - t).count(); };
+    const clk::time_point t_pass = clk::now();
+    stats_ = PassStats();
     std::vector<KeyFrameView*> vpKFs = mpMap->GetAllKeyFrames();
     changed_.clear();
-    // the images of the key frames that will be reconstructed in this pass first, so that the upload stream runs ahead
-    // of the compute stream
+    std::vector<KeyFrameView*> recon;  // PM.cc:141-142, 160
     for (KeyFrameView* kf : vpKFs)
-        if (!kf->isBad() && !kf->semidense_flag_ && (int)pick_neighbours(kf).size() >= covis_n_) make_resident(kf);
-    for (KeyFrameView* kf : vpKFs) SemiDenseRecon(kf);
+        if (!kf->isBad() && !kf->semidense_flag_ && (int)pick_neighbours(kf).size() >= covis_n_) recon.push_back(kf);
+    const size_t window = inplace_ ? std::max<size_t>(recon.size(), 1) : window_;
 
-    // PM.cc:262-313
-    for (size_t i = 0; i < vpKFs.size(); i++) {
-        KeyFrameView* kf = vpKFs[i];
-        if (kf->isBad() || kf->interKF_depth_flag_) continue;
-        if (!kf->semidense_flag_) continue;
-        std::vector<KeyFrameView*> neighbors = pick_neighbours(kf);
-        if ((int)neighbors.size() < covis_n_) continue;
-        int num_depth_kf = 0;
-        for (size_t j = 0; j < neighbors.size(); j++)
-            if (neighbors[j]->semidense_flag_) num_depth_kf++;
-        if (num_depth_kf < covis_n_) continue;
-        // InterKeyFrameDepthChecking + UpdateSemiDensePointSet (PM.cc:302-304): one fused launch
-        std::vector<int> ids;
-        kf->poseChanged = false;  // cleared BEFORE the pose is read: a SetPose that lands later raises it again (next pass)
-        make_resident(kf);
-        for (KeyFrameView* n : neighbors) {
-            make_resident(n);
-            ids.push_back(n->mnId);
+    struct Pending {
+        std::vector<Fetch> fetches;
+        int set = 0;
+        bool any = false;
+    } prev;
+    size_t pos = 0;
+    int turn = 0;
+    bool first = true;
+    while (first || pos < recon.size()) {
+        first = false;
+        const size_t end = std::min(recon.size(), pos + window);
+        std::unordered_set<int> in_window;
+        for (size_t r = pos; r < end; ++r) in_window.insert(recon[r]->mnId);
+        // the images of the window first, so that the upload stream runs ahead of the compute stream
+        clk::time_point t0 = clk::now();
+        for (size_t r = pos; r < end; ++r) make_resident(recon[r]);
+        stats_.resident += since(t0);
+        t0 = clk::now();
+        pos = end;
+
+        struct Entry {
+            KeyFrameView* kf;
+            std::vector<KeyFrameView*> nb;
+            std::vector<int> ids;
+            std::vector<float> rots;
+            float min_depth = 0, max_depth = 0;
+            bool recon = false, inter = false;
+        };
+        std::vector<Entry> entries;
+        for (KeyFrameView* kf : vpKFs) {  // list order = the visiting order of PM.cc:137 and PM.cc:262
+            if (kf->isBad() || kf->interKF_depth_flag_) continue;
+            const bool in_win = in_window.count(kf->mnId) != 0;
+            if (!in_win && !kf->semidense_flag_) continue;
+            std::vector<KeyFrameView*> nb = pick_neighbours(kf);
+            if ((int)nb.size() < covis_n_) continue;  // PM.cc:160, 287
+            bool inter = true;                        // PM.cc:289-297: every neighbour has (or gets in this window) its maps
+            for (KeyFrameView* n : nb)
+                if (!n->semidense_flag_ && !in_window.count(n->mnId)) inter = false;
+            if (!in_win && !inter) continue;
+            Entry e;
+            e.kf = kf; e.recon = in_win; e.inter = inter; e.nb = nb;
+            for (KeyFrameView* n : nb) {
+                e.ids.push_back(n->mnId);
+                if (in_win) e.rots.push_back(MedianRotInPlane(kf, n));  // PM.cc:170-179
+            }
+            if (in_win) StereoSearchConstraints(kf, &e.min_depth, &e.max_depth);  // PM.cc:184
+            entries.push_back(std::move(e));
         }
-        check(sd_interkf_check_points(ctx_, kf->mnId, ids.data(), (int)ids.size()), "sd_interkf_check_points");
-        kf->interKF_depth_flag_ = true;
-        if (std::find(changed_.begin(), changed_.end(), kf) == changed_.end()) changed_.push_back(kf);
+        stats_.prepare += since(t0);
+        t0 = clk::now();
+        // residency and poses of everything the window touches (uploads of neighbours outside the window, pose pushes,
+        // re-installation of released key frames)
+        for (Entry& e : entries) {
+            if (e.inter) e.kf->poseChanged = false;  // cleared BEFORE the pose is read: a later SetPose raises it again
+            KfState& st = make_resident(e.kf);
+            if (e.recon) st.imported = false;
+        }
+        for (Entry& e : entries)
+            for (KeyFrameView* n : e.nb) make_resident(n);
+
+        stats_.resident += since(t0);
+        t0 = clk::now();
+        join_expander();  // it reads the buffer set this window is about to overwrite (at the latest: normally long done)
+        stats_.expand += since(t0);
+        t0 = clk::now();
+        BufferSet& bs = bufs_[turn & 1];
+        std::vector<SdLoopItem> items(entries.size());
+        std::vector<int> inter_done(entries.size(), 0);
+        Pending cur;
+        cur.set = turn & 1;
+        if (!entries.empty()) {
+            const KeyFrameView* k0 = entries[0].kf;
+            const int record_cap = std::max(1, (int)(((size_t)k0->im_.rows * k0->im_.cols) / 2));
+            ensure_buffers(bs, std::max(entries.size(), window_), record_cap);
+        }
+        for (size_t i = 0; i < entries.size(); ++i) {
+            Entry& e = entries[i];
+            SdLoopItem& it = items[i];
+            std::memset(&it, 0, sizeof(it));
+            it.kf_id = e.kf->mnId;
+            it.nbr_ids = e.ids.data();
+            it.nbr_rot_deg = e.recon ? e.rots.data() : nullptr;
+            it.n = (int)e.ids.size();
+            it.min_invdepth = e.min_depth;
+            it.max_invdepth = e.max_depth;
+            it.finish_only = e.recon ? 0 : 1;
+            Fetch f;
+            f.kf = e.kf; f.points = e.inter; f.slot = (int)i;
+            f.sync_fallback = resident_.at(e.kf->mnId).imported;
+            if (f.sync_fallback) {
+                it.download = SD_DL_NONE;
+            } else {
+                it.download = e.inter ? SD_DL_COMPACT_POINTS : SD_DL_COMPACT;
+                it.out_records = static_cast<char*>(bs.base) + (size_t)i * bs.record_cap * sizeof(SdCompactPoint);
+                it.capacity = bs.record_cap;
+                it.out_count = bs.counts + i;
+                bs.counts[i] = -1;
+            }
+            cur.fetches.push_back(f);
+        }
+        if (!items.empty()) {
+            check(sd_semidense_loop(ctx_, items.data(), (int)items.size(), SD_LOOP_INTERKF, inter_done.data()), "sd_semidense_loop");
+            cur.any = true;
+            for (size_t i = 0; i < entries.size(); ++i) {
+                Entry& e = entries[i];
+                if (e.recon) e.kf->semidense_flag_ = true;  // PM.cc:244
+                if (e.inter != (inter_done[i] != 0)) {
+                    // the device knows better which neighbours have maps (e.g. flags reset by the caller): take its
+                    // word and fetch this key frame the direct way
+                    cur.fetches[i].sync_fallback = true;
+                    cur.fetches[i].points = inter_done[i] != 0;
+                }
+                if (inter_done[i]) e.kf->interKF_depth_flag_ = true;  // PM.cc:306
+            }
+        }
+        // the previous window's records are in host memory (sd_sync below, one iteration ago): expand them while the GPU
+        // works on this window
+        stats_.issue += since(t0);
+        t0 = clk::now();
+        // the previous window's records are in host memory (the sd_sync of the last iteration): a second thread expands
+        // them while this one waits for the GPU and then prepares and issues the next window
+        if (prev.any) expand_window(bufs_[prev.set], prev.fetches);
+        stats_.expand += since(t0);
+        t0 = clk::now();
+        if (cur.any) check(sd_sync(ctx_), "sd_sync");
+        stats_.sync += since(t0);
+        stats_.windows++;
+        prev = std::move(cur);
+        ++turn;
     }
-    // results back to the KeyFrame members, as the reference leaves them (PM.cc:225-226, 306, 361-363): only what
-    // this pass produced
-    for (KeyFrameView* kf : changed_)
-        if (!kf->isBad()) FetchResults(kf, kf->interKF_depth_flag_);
-    changed_.clear();
+    clk::time_point t1 = clk::now();
+    if (prev.any) expand_window(bufs_[prev.set], prev.fetches);
+    join_expander();
+    stats_.expand += since(t1);
     enforce_resident_limit(vpKFs);
     max_resident_seen_ = std::max(max_resident_seen_, resident_.size());
     passes_++;
+    stats_.total = since(t_pass);
+}
+
+void ProbabilityMapping::join_expander() {
+    if (expander_.joinable()) expander_.join();
+    if (expander_error_) {
+        std::exception_ptr e = expander_error_;
+        expander_error_ = nullptr;
+        std::rethrow_exception(e);
+    }
+}
+
+// Starts the expansion of one window's records on the expander thread (which fans out over `expand_threads_` workers) and
+// returns.  What needs the context -- key frames fetched the direct way -- is done here, on the calling thread, first.
+void ProbabilityMapping::expand_window(const BufferSet& b, const std::vector<Fetch>& fetches) {
+    join_expander();
+    struct Job {
+        KeyFrameView* kf;
+        const void* rec;
+        int n;
+        bool points;
+        std::vector<uint32_t>* filled;
+    };
+    std::vector<Job> jobs;
+    for (const Fetch& f : fetches) {
+        if (f.kf->isBad()) continue;
+        if (f.sync_fallback || b.counts[f.slot] < 0 || b.counts[f.slot] > b.record_cap) {
+            FetchResults(f.kf, f.points);  // imported maps, or more records than the window's buffers hold: the direct way
+            continue;
+        }
+        const char* rec = static_cast<const char*>(b.base) + (size_t)f.slot * b.record_cap * sizeof(SdCompactPoint);
+        jobs.push_back(Job{f.kf, rec, b.counts[f.slot], f.points, &filled_[f.kf->mnId]});  // the map is only touched here
+    }
+    if (jobs.empty()) return;
+    unsigned nt = expand_threads_ ? expand_threads_ : std::min(16u, std::max(1u, std::thread::hardware_concurrency()));
+    nt = (unsigned)std::min<size_t>(nt, jobs.size());
+    expander_ = std::thread([this, nt, jobs = std::move(jobs)] {
+        try {
+            std::atomic<size_t> next{0};
+            auto body = [&] {
+                for (size_t w = next++; w < jobs.size(); w = next++)
+                    expand_streaming(jobs[w].kf, jobs[w].rec, jobs[w].n, jobs[w].points, *jobs[w].filled);
+            };
+            std::vector<std::thread> pool;
+            for (unsigned t = 1; t < nt; ++t) pool.emplace_back(body);
+            body();
+            for (std::thread& t : pool) t.join();
+        } catch (...) {
+            expander_error_ = std::current_exception();
+        }
+    });
+}
+
+namespace {
+// dst <- src with stores that bypass the cache (the planes are written once and not read back here)
+void stream_copy(float* dst, const float* src, size_t n) {
+#if defined(__SSE2__)
+    if (((reinterpret_cast<uintptr_t>(dst) | reinterpret_cast<uintptr_t>(src)) & 15u) == 0) {
+        size_t i = 0;
+        for (; i + 4 <= n; i += 4) _mm_stream_ps(dst + i, _mm_load_ps(src + i));
+        for (; i < n; ++i) dst[i] = src[i];
+        return;
+    }
+#endif
+    std::memcpy(dst, src, n * sizeof(float));
+}
+struct AlignedFloats {
+    float* p = nullptr;
+    size_t n = 0;
+    ~AlignedFloats() { std::free(p); }
+    float* get(size_t want) {
+        if (want > n) {
+            std::free(p);
+            p = static_cast<float*>(std::aligned_alloc(64, (want * sizeof(float) + 63) / 64 * 64));
+            if (!p) throw std::bad_alloc();
+            n = want;
+        }
+        return p;
+    }
+};
+}  // namespace
+
+// Compact records -> the dense members (PM.cc:225-226, 361-363), written as whole planes in bands of 16 rows: the
+// records are bucketed by band (they arrive in no particular order), each band is assembled in a cache-resident staging
+// buffer (zeros + the band's records) and streamed to the member once.  Memory traffic is one write of every plane,
+// instead of the read-for-ownership + write-back of nearly every cache line, twice (clear, then write), that a scatter
+// straight into the members costs.
+void ProbabilityMapping::expand_streaming(KeyFrameView* kf, const void* records, int n, bool points, std::vector<uint32_t>& filled) {
+    const int W = kf->im_.cols, H = kf->im_.rows;
+    const size_t px = (size_t)W * H;
+    if (kf->depth_map_.size() != px) kf->depth_map_.assign(px, 0.0f);
+    if (kf->depth_sigma_.size() != px) kf->depth_sigma_.assign(px, 0.0f);
+    const bool had_points = kf->SemiDensePointSets_.size() == 3 * px;
+    if (points && !had_points) kf->SemiDensePointSets_.assign(3 * px, 0.0f);
+    // a key frame that has a point set from an earlier pass and gets maps without points now: the stale points of the
+    // pixels written last time go, as in expand_records
+    const bool clear_points = !points && had_points;
+    constexpr int BH = 16;
+    const int nb = (H + BH - 1) / BH;
+    const size_t stride = points ? sizeof(SdCompactPoint) : sizeof(SdCompactDepth);
+    const char* rec = static_cast<const char*>(records);
+    auto pixel_of = [&](int i) { return *reinterpret_cast<const uint32_t*>(rec + (size_t)i * stride); };
+    thread_local std::vector<int> start, order;
+    thread_local AlignedFloats stage;
+    start.assign((size_t)nb + 1, 0);
+    for (int i = 0; i < n; ++i) {
+        const uint32_t p = pixel_of(i);
+        const int y = (int)(p >> 16), x = (int)(p & 0xffffu);
+        if (y >= H || x >= W) throw std::runtime_error("expand_streaming: record outside the image");
+        start[(size_t)y / BH + 1]++;
+    }
+    for (int b = 0; b < nb; ++b) start[(size_t)b + 1] += start[b];
+    order.resize((size_t)n);
+    {
+        std::vector<int> at(start.begin(), start.end() - 1);
+        for (int i = 0; i < n; ++i) order[(size_t)at[(pixel_of(i) >> 16) / BH]++] = i;
+    }
+    if (clear_points)
+        for (uint32_t e : filled) {
+            const size_t o = (size_t)(e >> 16) * W + (e & 0xffffu);
+            kf->SemiDensePointSets_[3 * o] = 0.0f; kf->SemiDensePointSets_[3 * o + 1] = 0.0f; kf->SemiDensePointSets_[3 * o + 2] = 0.0f;
+        }
+    const size_t band_px = (size_t)BH * W;
+    float* sd = stage.get(band_px * (points ? 5 : 2) + 64);
+    float* ss = sd + (band_px + 15) / 16 * 16;
+    float* sp = ss + (band_px + 15) / 16 * 16;
+    for (int b = 0; b < nb; ++b) {
+        const int y0 = b * BH, rows = std::min(BH, H - y0);
+        const size_t cnt = (size_t)rows * W;
+        std::memset(sd, 0, cnt * sizeof(float));
+        std::memset(ss, 0, cnt * sizeof(float));
+        if (points) std::memset(sp, 0, 3 * cnt * sizeof(float));
+        for (int k = start[b]; k < start[(size_t)b + 1]; ++k) {
+            const char* r = rec + (size_t)order[(size_t)k] * stride;
+            const SdCompactDepth* d = reinterpret_cast<const SdCompactDepth*>(r);  // SdCompactPoint begins with the same three fields
+            const size_t o = (size_t)((int)(d->pixel >> 16) - y0) * W + (d->pixel & 0xffffu);
+            sd[o] = d->depth;
+            ss[o] = d->sigma;
+            if (points) {
+                const SdCompactPoint* q = reinterpret_cast<const SdCompactPoint*>(r);
+                sp[3 * o] = q->x; sp[3 * o + 1] = q->y; sp[3 * o + 2] = q->z;
+            }
+        }
+        const size_t off = (size_t)y0 * W;
+        stream_copy(kf->depth_map_.data() + off, sd, cnt);
+        stream_copy(kf->depth_sigma_.data() + off, ss, cnt);
+        if (points) stream_copy(kf->SemiDensePointSets_.data() + 3 * off, sp, 3 * cnt);
+    }
+#if defined(__SSE2__)
+    _mm_sfence();
+#endif
+    filled.resize((size_t)n);
+    for (int i = 0; i < n; ++i) filled[(size_t)i] = pixel_of(i);
 }
 
 void ProbabilityMapping::SemiDenseRecon(KeyFrameView* kf) {
@@ -342,7 +639,13 @@ void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
     if ((int)records_.size() < cap) records_.resize(cap);
     int n = 0;
     check(sd_download_compact(ctx_, kf->mnId, points ? 1 : 0, cap, records_.data(), &n), "sd_download_compact");
-    std::vector<uint32_t>& filled = filled_[kf->mnId];
+    expand_records(kf, records_.data(), n, points, filled_[kf->mnId]);
+}
+
+// Compact records -> the dense members the reference leaves in the KeyFrame (PM.cc:225-226, 361-363).  `filled` lists the
+// pixels the previous expansion of this key frame wrote: only those are cleared, instead of the whole planes.
+void ProbabilityMapping::expand_records(KeyFrameView* kf, const void* records, int n, bool points, std::vector<uint32_t>& filled) {
+    const size_t px = (size_t)kf->im_.rows * kf->im_.cols;
     const int W = kf->im_.cols;
     const bool fresh_maps = kf->depth_map_.size() != px || kf->depth_sigma_.size() != px;
     if (fresh_maps) {
@@ -362,7 +665,7 @@ void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
     }
     filled.resize(n);
     if (points) {
-        const SdCompactPoint* r = records_.data();
+        const SdCompactPoint* r = static_cast<const SdCompactPoint*>(records);
         for (int i = 0; i < n; ++i) {
             const size_t o = (size_t)(r[i].pixel >> 16) * W + (r[i].pixel & 0xffffu);
             kf->depth_map_[o] = r[i].depth;
@@ -371,7 +674,7 @@ void ProbabilityMapping::FetchResults(KeyFrameView* kf, bool points) {
             filled[i] = r[i].pixel;
         }
     } else {
-        const SdCompactDepth* r = reinterpret_cast<const SdCompactDepth*>(records_.data());
+        const SdCompactDepth* r = static_cast<const SdCompactDepth*>(records);
         for (int i = 0; i < n; ++i) {
             const size_t o = (size_t)(r[i].pixel >> 16) * W + (r[i].pixel & 0xffffu);
             kf->depth_map_[o] = r[i].depth;

@@ -26,8 +26,10 @@
 
 #include <atomic>
 #include <cstdint>
+#include <exception>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -173,6 +175,15 @@ public:
     // again (a later key frame lists it, or its pose changes, PM.cc:321-334) is re-installed from its host members --
     // then with the CHECKED inverse depth, which is what the reference's in-place depth_map_ holds by that time.
     void SetResidentLimit(size_t n) { resident_limit_ = n; }
+    // SemiDenseLoop issues a pass in windows of at most `n` key frames to reconstruct: one sd_semidense_loop call per
+    // window with the compact records of every key frame it completes downloaded asynchronously into page-locked
+    // buffers (two sets of n), expanded into the KeyFrame members by `threads` host threads while the GPU works on the
+    // next window.  n bounds the page-locked memory (n * W*H/2 * 24 bytes per set); 0 threads = hardware concurrency,
+    // at most 16.  With SdParams.interkf_inplace a pass is one window (the checks are order-dependent).
+    void SetBatchWindow(size_t n, unsigned threads = 0) { window_ = n ? n : 1; expand_threads_ = threads; }
+    // Host wall-clock seconds of the last SemiDenseLoop pass by phase (diagnostics of the e2e_class bench leg).
+    struct PassStats { double resident = 0, prepare = 0, issue = 0, expand = 0, sync = 0, total = 0; int windows = 0; };
+    const PassStats& LastPassStats() const { return stats_; }
     void ReleaseKeyFrame(KeyFrameView* kf);
     size_t ResidentKeyFrames() const { return resident_.size(); }
     size_t MaxResidentKeyFrames() const { return max_resident_seen_; }  // high-water mark after the release step of a pass
@@ -184,8 +195,25 @@ private:
         float Tcw[12];                 // the pose the device holds
         bool imported = false;         // maps re-installed from the host members (no compact form)
     };
+    struct Fetch {                     // one asynchronous compact download of a window
+        KeyFrameView* kf = nullptr;
+        bool points = false;
+        int slot = 0;                  // buffer of the set
+        bool sync_fallback = false;    // imported maps (no compact form): fetched the slow way after the window
+    };
+    struct BufferSet {
+        void* base = nullptr;          // page-locked, slots * record_cap * sizeof(SdCompactPoint)
+        int* counts = nullptr;         // page-locked, one per slot
+        size_t slots = 0;
+        int record_cap = 0;
+    };
     bool CheckFinish();
     void SetFinish();
+    void ensure_buffers(BufferSet& b, size_t slots, int record_cap);
+    void expand_window(const BufferSet& b, const std::vector<Fetch>& fetches);
+    void expand_records(KeyFrameView* kf, const void* records, int n, bool points, std::vector<uint32_t>& filled);
+    static void expand_streaming(KeyFrameView* kf, const void* records, int n, bool points, std::vector<uint32_t>& filled);
+    void join_expander();
     KfState& make_resident(KeyFrameView* kf);  // upload on first use, push the pose if it moved, re-install released maps
     std::vector<KeyFrameView*> pick_neighbours(KeyFrameView* kf) const;  // PM.cc:151-160, 278-287
     void enforce_resident_limit(const std::vector<KeyFrameView*>& vpKFs);
@@ -199,6 +227,13 @@ private:
     std::vector<KeyFrameView*> changed_;              // results to copy back at the end of the pass
     std::vector<SdCompactPoint> records_;             // download scratch
     size_t resident_limit_ = 0, max_resident_seen_ = 0;
+    size_t window_ = 16;
+    unsigned expand_threads_ = 0;
+    bool inplace_ = false;                            // SdParams.interkf_inplace of the context
+    BufferSet bufs_[2];
+    PassStats stats_;
+    std::thread expander_;                            // expands the previous window's records while this thread issues the next
+    std::exception_ptr expander_error_;
     std::atomic<uint64_t> passes_{0};
     std::string obj_path_ = "semi_pointcloud.obj";
     std::mutex mMutexFinish;

@@ -9,6 +9,10 @@
 //        `limit` > 0 bounds the key frames resident on the device (SetResidentLimit)
 //   test_pm_class --stale-pose <scene.bin> <out.bin>   uploads every key frame with a WRONG pose first, then SetPose(true
 //        pose) and one pass: the results must be those of the true poses (the reference reads poses at call time)
+//   test_pm_class --bench=steps[,warmup[,window[,threads]]] <scene.bin> <out.bin>
+//        bench.py's `e2e_class` leg: `steps` timed passes of SemiDenseLoop over the whole map, every pass from scratch
+//        (key frames released and flags cleared, so that images are uploaded and results expanded into the KeyFrame
+//        members again, as in a first pass); prints one line `bench: {json}`; out.bin as in the plain mode (last pass)
 //   test_pm_class --no-device-check                  exits 0 iff construction fails loudly without a GPU
 //
 // scene.bin (little endian): int32 nkf, w, h, covis_n; then per key frame:
@@ -19,6 +23,8 @@
 //   float points[3*w*h] if has_points; then per probe: float depth, sigma, best_u, best_v, supported, umin, umax
 #include <unistd.h>
 
+#include <algorithm>
+#include <chrono>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -59,6 +65,7 @@ int main(int argc, char** argv) {
         return 0;
     }
     bool stream = false, stale_pose = false;
+    int bench_steps = 0, bench_warmup = 1, bench_window = 16, bench_threads = 0;
     long limit = 0;
     if (argc >= 2 && !std::strncmp(argv[1], "--stream", 8)) {
         stream = true;
@@ -66,6 +73,10 @@ int main(int argc, char** argv) {
         --argc; ++argv;
     } else if (argc >= 2 && !std::strcmp(argv[1], "--stale-pose")) {
         stale_pose = true;
+        --argc; ++argv;
+    } else if (argc >= 2 && !std::strncmp(argv[1], "--bench=", 8)) {
+        std::sscanf(argv[1] + 8, "%d,%d,%d,%d", &bench_steps, &bench_warmup, &bench_window, &bench_threads);
+        if (bench_steps < 1) bench_steps = 1;
         --argc; ++argv;
     }
     if (argc < 3) {
@@ -163,6 +174,30 @@ int main(int argc, char** argv) {
                         pm.ResidentKeyFrames(), pm.MaxResidentKeyFrames(), limit);
             if (limit > 0 && (long)pm.MaxResidentKeyFrames() > limit + 3 * covis_n + 1)
                 throw std::runtime_error("resident limit not enforced");
+        } else if (bench_steps > 0) {
+            for (int i = 0; i < nkf; ++i) map.AddKeyFrame(kfs[i].get());
+            pm.SetBatchWindow((size_t)bench_window, (unsigned)bench_threads);
+            auto one_pass = [&] {
+                for (int i = 0; i < nkf; ++i) {
+                    pm.ReleaseKeyFrame(kfs[i].get());
+                    kfs[i]->semidense_flag_ = false;
+                    kfs[i]->interKF_depth_flag_ = false;
+                }
+                pm.SemiDenseLoop();
+            };
+            for (int i = 0; i < std::max(bench_warmup, 1); ++i) one_pass();  // first pass also allocates the KeyFrame members
+            const auto t0 = std::chrono::steady_clock::now();
+            for (int i = 0; i < bench_steps; ++i) one_pass();
+            const double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+            int done = 0;
+            for (int i = 0; i < nkf; ++i) done += kfs[i]->interKF_depth_flag_ ? 1 : 0;
+            const ProbabilityMapping::PassStats& ps = pm.LastPassStats();
+            std::printf("last pass: %d windows, resident %.1f ms, prepare %.1f ms, issue %.1f ms, expand %.1f ms, sync %.1f ms, total %.1f ms\n",
+                        ps.windows, 1e3 * ps.resident, 1e3 * ps.prepare, 1e3 * ps.issue, 1e3 * ps.expand, 1e3 * ps.sync, 1e3 * ps.total);
+            std::printf("bench: {\"keyframes\": %d, \"steps\": %d, \"warmup\": %d, \"window\": %d, \"seconds\": %.6f, "
+                        "\"kf_per_s\": %.2f, \"ms_per_step\": %.3f, \"inter_checked\": %d}\n",
+                        nkf, bench_steps, std::max(bench_warmup, 1), bench_window, sec, bench_steps * (double)nkf / sec,
+                        1e3 * sec / bench_steps, done);
         } else {
             for (int i = 0; i < nkf; ++i) map.AddKeyFrame(kfs[i].get());
             if (stale_pose) {

@@ -243,3 +243,25 @@ def test_intra_grow_planes(ctx, po, h, w):
     depth2, sigma2, grad2 = _crafted_planes(np.random.default_rng(7), h, w, False)
     gd2, gs2 = ctx.intra_planes(depth2, sigma2, grad2, grow=True)
     assert np.array_equal(gd2, depth2) and np.array_equal(gs2, sigma2)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("window,threads", [(5, 3), (64, 1)])
+def test_class_windowed_passes_equal_oracle(tmp_path, pkg, po, synth, pipeline, window, threads):
+    """SemiDenseLoop issues a pass in windows (one sd_semidense_loop call each, asynchronous compact downloads, records
+    expanded by host threads while the GPU runs the next window).  Three passes from scratch over a 24-key-frame map, in
+    windows of 5 (key frames whose neighbours fall into a later window get their inter-key-frame check there) and in a
+    single window: the KeyFrame members after the last pass are the oracle's, bit for bit (expansion over members that
+    already hold the previous pass's values included).  This is the mode bench.py's `e2e_class` leg times."""
+    import json
+    scene, plan, images, rots, _, scene_path = _host_scene(tmp_path, synth, pipeline, nkf=24, n=5, seed=35, with_probes=False)
+    out_path = tmp_path / "out.bin"
+    r = subprocess.run([DRIVER, f"--bench=2,1,{window},{threads}", str(scene_path), str(out_path)], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("bench: ")][0]
+    b = json.loads(line[len("bench: "):])
+    assert b["keyframes"] == 24 and b["inter_checked"] == 24 and b["kf_per_s"] > 0
+    ora = _oracle_run(po, scene, plan, images, rots)
+    raw = np.fromfile(out_path, np.uint8)
+    off, _ = _check_maps(raw, scene, plan, ora, po)
+    assert off == raw.size

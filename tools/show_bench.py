@@ -14,3 +14,5 @@ for r in d.get("per_rank", []):
         print("     timeline device", r["timeline"]["device_ms"], " host", r["timeline"]["host_issue_ms"])
 if d.get("roofline", {}).get("issue"):
     print("  issue roofline", {k: (round(v, 3) if isinstance(v, float) else v) for k, v in d["roofline"]["issue"].items() if k != "source"})
+if "e2e_class" in d:
+    print("  e2e_class", {k: v for k, v in d["e2e_class"].items() if k != "what"})
