@@ -68,7 +68,8 @@ def parse():
     ap.add_argument("--no-configs", action="store_true", help="skip the short runs of BASELINE configs 1, 3, 5")
     ap.add_argument("--no-seam-check", action="store_true")
     ap.add_argument("--no-class-leg", action="store_true", help="skip e2e_class (the C++ drop-in class driven by lib/test_pm_class --bench)")
-    ap.add_argument("--class-window", type=int, default=16, help="key frames per sd_semidense_loop call of ProbabilityMapping::SemiDenseLoop")
+    ap.add_argument("--class-window", type=int, default=32, help="key frames per sd_semidense_loop call of ProbabilityMapping::SemiDenseLoop")
+    ap.add_argument("--class-threads", type=int, default=0, help="host threads that expand records into the KeyFrame members (0 = all cores, at most 16)")
     ap.add_argument("--seed", type=int, default=1234)
     return ap.parse_args()
 
@@ -760,7 +761,7 @@ def class_leg(args, scene_path, nkf):
     out_path = os.path.join(os.path.dirname(scene_path), "class_out.bin")
     steps = max(2, min(args.steps, 5))
     try:
-        r = subprocess.run([driver, f"--bench={steps},2,{args.class_window},0", scene_path, out_path], capture_output=True, text=True, timeout=600)
+        r = subprocess.run([driver, f"--bench={steps},2,{args.class_window},{args.class_threads}", scene_path, out_path], capture_output=True, text=True, timeout=600)
         got = [ln for ln in r.stdout.splitlines() if ln.startswith("bench: ")]
         if r.returncode != 0 or not got:
             return {"unavailable": (r.stderr or r.stdout).strip()[-300:]}

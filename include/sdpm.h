@@ -212,6 +212,14 @@ int sd_halo_exchange(sd_ctx* ctx, const SdHaloPeer* peers, int n_peers);
 int sd_alloc_host(sd_ctx* ctx, uint64_t bytes, void** out);
 int sd_free_host(sd_ctx* ctx, void* ptr);
 
+/* Wait for downloads without waiting for the rest of the GPU's queue (sd_sync waits for everything).  sd_download_fence
+ * returns a ticket that stands for every asynchronous download queued on the context so far (SdLoopItem downloads,
+ * sd_download_async, sd_download_compact_async); sd_download_wait(ticket) returns once those have landed in their host
+ * buffers and their counts are written, while later work -- the next window of key frames -- keeps running.  This is how
+ * ProbabilityMapping::SemiDenseLoop keeps two windows in flight.  (No reference counterpart.) */
+int sd_download_fence(sd_ctx* ctx, uint64_t* ticket);
+int sd_download_wait(sd_ctx* ctx, uint64_t ticket);
+
 int sd_sync(sd_ctx* ctx);
 const char* sd_last_error(sd_ctx* ctx);
 /* cudaStream_t of the compute stream, for callers that order their own device work after it */

@@ -98,6 +98,8 @@ SYMBOLS = {
     "sd_export_maps": (C.c_int, [_vp, C.c_int, _vp, _vp]),
     "sd_alloc_host": (C.c_int, [_vp, C.c_uint64, C.POINTER(_vp)]),
     "sd_free_host": (C.c_int, [_vp, _vp]),
+    "sd_download_fence": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "sd_download_wait": (C.c_int, [_vp, C.c_uint64]),
     "sd_sync": (C.c_int, [_vp]),
     "sd_last_error": (C.c_char_p, [_vp]),
     "sd_compute_stream": (C.c_int, [_vp, C.POINTER(_vp)]),

@@ -78,7 +78,7 @@ struct sd_ctx {
     // highest record number of the producing stream that the consuming stream has already waited for
     long long srch_seen_up = 0, main_seen_up = 0, chk_seen_sd = 0, dn_seen_sd = 0, main_seen_chk = -1, dn_seen_chk = -1;
     bool dirty = false;  // work has been queued on s_srch / s_main / s_chk / s_dn since s_up last waited for those streams
-    cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr;
+    cudaEvent_t ev_tmp = nullptr, ev_span_a = nullptr, ev_span_b = nullptr, ev_fence = nullptr;
     std::unordered_map<int, Slot*> kfs;
     std::vector<Slot*> free_slots;
     // k1_fuse output / k23_intra input, one pair per hypothesis buffer; invariant: all zero while no key frame is in
@@ -528,6 +528,7 @@ int sd_destroy(sd_ctx* c) {
     if (c->ev_tmp) cudaEventDestroy(c->ev_tmp);
     if (c->ev_span_a) cudaEventDestroy(c->ev_span_a);
     if (c->ev_span_b) cudaEventDestroy(c->ev_span_b);
+    if (c->ev_fence) cudaEventDestroy(c->ev_fence);
     cudaFree(c->conf_state);
     cudaFree(c->conf_hist);
     cudaFree(c->conf_seg);
@@ -1368,6 +1369,30 @@ int sd_free_host(sd_ctx* c, void* ptr) {
     if (!ptr) return SD_OK;
     CU(c, cudaSetDevice(c->device));
     CU(c, cudaFreeHost(ptr));
+    return SD_OK;
+}
+
+int sd_download_fence(sd_ctx* c, uint64_t* ticket) {
+    if (!c || !ticket) return SD_ERR_INVALID_ARG;
+    *ticket = (uint64_t)c->pack_tail;
+    return SD_OK;
+}
+
+int sd_download_wait(sd_ctx* c, uint64_t ticket) {
+    if (!c || (long long)ticket > c->pack_tail) return fail(c, SD_ERR_INVALID_ARG, "sd_download_wait: ticket from the future");
+    CU(c, cudaSetDevice(c->device));
+    // compact downloads are two-step (count, then exactly that many records): issue the copies of everything up to the
+    // ticket, in order, as their counts arrive
+    while (c->pack_head < (long long)ticket) {
+        sd_ctx::PackSlot& ps = c->pack[c->pack_head % sd_ctx::PACK_RING];
+        CU(c, cudaEventSynchronize(ps.ev_cnt));
+        CU(c, pack_issue(c, c->pack_head));
+        c->pack_head++;
+    }
+    // every download runs on the one download stream, in order: an event behind the last copy covers the dense ones too
+    if (!c->ev_fence) CU(c, cudaEventCreateWithFlags(&c->ev_fence, cudaEventDisableTiming));
+    CU(c, cudaEventRecord(c->ev_fence, c->s_dn));
+    CU(c, cudaEventSynchronize(c->ev_fence));
     return SD_OK;
 }
 

@@ -198,6 +198,7 @@ void ProbabilityMapping::SemiDenseLoop() {
         std::vector<Fetch> fetches;
         int set = 0;
         bool any = false;
+        uint64_t ticket = 0;  // sd_download_fence after the window was issued
     } prev;
     size_t pos = 0;
     int turn = 0;
@@ -256,14 +257,13 @@ void ProbabilityMapping::SemiDenseLoop() {
 
         stats_.resident += since(t0);
         t0 = clk::now();
-        join_expander();  // it reads the buffer set this window is about to overwrite (at the latest: normally long done)
-        stats_.expand += since(t0);
-        t0 = clk::now();
-        BufferSet& bs = bufs_[turn & 1];
+        // three buffer sets: this window's set was last read by the expansion of three windows ago, which ended before
+        // the expansion of two windows ago started (expand_window joins its predecessor)
+        BufferSet& bs = bufs_[turn % 3];
         std::vector<SdLoopItem> items(entries.size());
         std::vector<int> inter_done(entries.size(), 0);
         Pending cur;
-        cur.set = turn & 1;
+        cur.set = turn % 3;
         if (!entries.empty()) {
             const KeyFrameView* k0 = entries[0].kf;
             const int record_cap = std::max(1, (int)(((size_t)k0->im_.rows * k0->im_.cols) / 2));
@@ -296,6 +296,7 @@ void ProbabilityMapping::SemiDenseLoop() {
         }
         if (!items.empty()) {
             check(sd_semidense_loop(ctx_, items.data(), (int)items.size(), SD_LOOP_INTERKF, inter_done.data()), "sd_semidense_loop");
+            check(sd_download_fence(ctx_, &cur.ticket), "sd_download_fence");
             cur.any = true;
             for (size_t i = 0; i < entries.size(); ++i) {
                 Entry& e = entries[i];
@@ -313,18 +314,24 @@ void ProbabilityMapping::SemiDenseLoop() {
         // works on this window
         stats_.issue += since(t0);
         t0 = clk::now();
-        // the previous window's records are in host memory (the sd_sync of the last iteration): a second thread expands
-        // them while this one waits for the GPU and then prepares and issues the next window
-        if (prev.any) expand_window(bufs_[prev.set], prev.fetches);
-        stats_.expand += since(t0);
-        t0 = clk::now();
-        if (cur.any) check(sd_sync(ctx_), "sd_sync");
-        stats_.sync += since(t0);
+        // two windows in flight: this one is queued behind the previous one on the GPU.  Wait for the previous window's
+        // downloads only (not for the queue), then hand its records to the expander thread and go on to prepare the next
+        // window while the GPU runs this one
+        if (prev.any) {
+            check(sd_download_wait(ctx_, prev.ticket), "sd_download_wait");
+            stats_.sync += since(t0);
+            t0 = clk::now();
+            expand_window(bufs_[prev.set], prev.fetches);
+            stats_.expand += since(t0);
+        }
         stats_.windows++;
         prev = std::move(cur);
         ++turn;
     }
     clk::time_point t1 = clk::now();
+    check(sd_sync(ctx_), "sd_sync");
+    stats_.sync += since(t1);
+    t1 = clk::now();
     if (prev.any) expand_window(bufs_[prev.set], prev.fetches);
     join_expander();
     stats_.expand += since(t1);

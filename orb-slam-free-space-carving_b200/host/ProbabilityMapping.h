@@ -177,7 +177,7 @@ public:
     void SetResidentLimit(size_t n) { resident_limit_ = n; }
     // SemiDenseLoop issues a pass in windows of at most `n` key frames to reconstruct: one sd_semidense_loop call per
     // window with the compact records of every key frame it completes downloaded asynchronously into page-locked
-    // buffers (two sets of n), expanded into the KeyFrame members by `threads` host threads while the GPU works on the
+    // buffers (three sets of n: one being filled by the GPU, one being expanded, one in between), expanded into the KeyFrame members by `threads` host threads while the GPU works on the
     // next window.  n bounds the page-locked memory (n * W*H/2 * 24 bytes per set); 0 threads = hardware concurrency,
     // at most 16.  With SdParams.interkf_inplace a pass is one window (the checks are order-dependent).
     void SetBatchWindow(size_t n, unsigned threads = 0) { window_ = n ? n : 1; expand_threads_ = threads; }
@@ -227,10 +227,10 @@ private:
     std::vector<KeyFrameView*> changed_;              // results to copy back at the end of the pass
     std::vector<SdCompactPoint> records_;             // download scratch
     size_t resident_limit_ = 0, max_resident_seen_ = 0;
-    size_t window_ = 16;
+    size_t window_ = 32;
     unsigned expand_threads_ = 0;
     bool inplace_ = false;                            // SdParams.interkf_inplace of the context
-    BufferSet bufs_[2];
+    BufferSet bufs_[3];
     PassStats stats_;
     std::thread expander_;                            // expands the previous window's records while this thread issues the next
     std::exception_ptr expander_error_;

@@ -65,7 +65,7 @@ int main(int argc, char** argv) {
         return 0;
     }
     bool stream = false, stale_pose = false;
-    int bench_steps = 0, bench_warmup = 1, bench_window = 16, bench_threads = 0;
+    int bench_steps = 0, bench_warmup = 1, bench_window = 32, bench_threads = 0;
     long limit = 0;
     if (argc >= 2 && !std::strncmp(argv[1], "--stream", 8)) {
         stream = true;
