@@ -355,7 +355,11 @@ class Workload:
         # outputs: ONE pinned staging area, viewed per leg (dense planes / compact records)
         px = W * H
         self.cap = int(record_fill * px)              # records per key frame the staging area holds (about 26 % carry anything)
-        per_kf = max(2 * px * 4, self.cap * pkg.COMPACT_POINT.itemsize)
+        per_kf = self.cap * pkg.COMPACT_DEPTH.itemsize                        # "e2e": compact records of the two maps
+        if "e2e_points" in legs:
+            per_kf = max(per_kf, self.cap * pkg.COMPACT_POINT.itemsize)
+        if "e2e_dense" in legs:
+            per_kf = max(per_kf, 2 * px * 4)
         self.out = torch.empty((len(self.owned), per_kf), dtype=torch.uint8).pin_memory()
         self.counts = torch.zeros((len(self.owned),), dtype=torch.int32).pin_memory()
         self.oslot = {k: i for i, k in enumerate(self.owned)}
@@ -460,6 +464,14 @@ def run_b200(args):
     pkg = load_package()
     synth = importlib.import_module(PKG_NAME + ".synth")
     sharding = importlib.import_module(PKG_NAME + ".sharding")
+    if world > 1:
+        # torchrun exports OMP_NUM_THREADS=1, which would render this rank's synthetic key frames (input generation,
+        # outside every timed region) on one core: give the generator this rank's share of the host instead
+        try:
+            import ctypes
+            ctypes.CDLL("libgomp.so.1").omp_set_num_threads(max(1, host_cores() // (1 if numa else world)))
+        except Exception:
+            pass
 
     ctx = pkg.Context(local)
     if world > 1:   # the path's own communicator: rank 0 draws the id, torch.distributed only carries the 128 bytes
@@ -656,6 +668,18 @@ def run_b200(args):
         line["e2e_class"] = class_leg(args, class_scene, args.nkf)
     if rank == 0 and world == 1 and not args.no_configs:
         line["configs"] = other_configs(args, torch, pkg, synth, sharding, dev)
+    if world > 1 and not args.no_configs:
+        cfgs = sharded_configs(args, torch, dist, dev, pkg, synth, sharding, world, rank, local)
+        if rank == 0:
+            line["configs"] = cfgs
+    if rank == 0 and world > 1 and not args.no_cpu_baseline:   # every line carries the CPU leg; the other ranks wait at the barrier below
+        from oracle import pm_oracle as po
+        threads = host_cores()
+        sample = max(args.cpu_sample, n + 1)
+        _, plan, images = cpu_sample_plan(args, synth, po, sample)
+        dt = cpu_pass(po, plan, images, threads)
+        line["cpu_baseline"] = {"value": sample / dt, "unit": UNIT, "cores": threads, "kind": "port",
+                                "sample": f"first {sample} key frames of the same workload, all stages K0..K5, oracle port with OpenMP on the reference's five pragma loops (one pass, {dt:.1f} s), rank 0's host only"}
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         from oracle import pm_oracle as po
         threads = host_cores()
@@ -684,7 +708,7 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank):
+def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank, only=None, threads=None):
     """Every rank: the owned key frames with neighbours on another rank -- the first and last N/2 of its range -- against the
     CPU oracle run on the window around the seam, DEPTH / SIGMA / DEPTH_CHECKED bitwise (the loop being sharded is
     PM.cc:262-307, the reads across the seam PM.cc:705-752).  Returns the all-reduced counts."""
@@ -692,6 +716,8 @@ def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank):
     ctx, n, total = wl.ctx, wl.n, wl.total_kf
     own = set(wl.owned)
     seam = [k for k in wl.owned if any(int(j) not in own for j in wl.plan.nbrs[k])]
+    if only is not None:   # a subset (long neighbour lists make the oracle window expensive): only(rank, seam) -> key frames
+        seam = list(only(rank, seam))
     plan = HostPlan(synth, wl.scene, total, n, [], po.stereo_search_constraints, args.prior_sigmas)
     need_sd = set(seam)
     for k in seam:
@@ -703,7 +729,7 @@ def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank):
         need_img.update(int(j) for j in plan.nbrs[k])
     hnp = wl.host_img.numpy()
     images = {k: (hnp[wl.slot[k]] if k in wl.slot else wl.scene.render(k)) for k in sorted(need_img)}
-    ora = po.Oracle(threads=max(1, host_cores() // world))
+    ora = po.Oracle(threads=threads or max(1, host_cores() // world))
     for k in sorted(need_img):
         ora.add_keyframe(k, images[k], wl.scene.K, wl.scene.pose(k))
     for k in sorted(need_sd):
@@ -720,6 +746,54 @@ def seam_parity(args, torch, dist, dev, pkg, synth, wl, world, rank):
     dist.all_reduce(t, op=dist.ReduceOp.SUM)
     return {"keyframes_checked": int(t[0].item()), "planes": 3, "mismatching": int(t[1].item()),
             "checker": "CPU oracle on the +-N window around every seam, bitwise", "ranks": world}
+
+
+def sharded_configs(args, torch, dist, dev, pkg, synth, sharding, world, rank, local):
+    """world > 1: BASELINE configs[2] AS STATED -- 1 000 key frames in total, N = 20, sharded over the ranks (strong
+    scaling: 1000 / world key frames per rank, a 10-key-frame halo per side) -- and configs[4] (1080p, prior widened to
+    mean +- 4 sigma, N = 5 and N = 40, 24 key frames per rank), 2 timed steps each after 1 warm-up, device time = max over
+    ranks of the span over all of the context's streams.  Config 3 carries its own seam check: the key frame on either side
+    of the seam between ranks 0 and 1 against the CPU oracle (a 21-key-frame window each at N = 20)."""
+    peak, _, _ = measured_peaks()
+    out = {}
+    for name, cam, per_rank, n, sig, scaling in (("config3_720p_n20_1000kf", "720p", 1000 // world, 20, 2.0, "strong"),
+                                                 ("config5_1080p_n5", "1080p", 24, 5, 4.0, "weak"),
+                                                 ("config5_1080p_n40", "1080p", 24, 40, 4.0, "weak")):
+        c = pkg.Context(local)
+        ids = [pkg.nccl_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, device=dev)
+        c.comm_init(world, rank, ids[0])
+        w = Workload(torch, pkg, synth, sharding, c, dev, cam, per_rank, n, world, rank, args.seed, sig, legs=("value", "e2e"), record_fill=0.6)
+        res, steps = {}, 2
+        for leg in ("value", "e2e"):
+            w.step(leg)
+            c.sync()
+            dist.barrier()
+            torch.cuda.synchronize()
+            c.span_begin()
+            for _ in range(steps):
+                w.step(leg)
+            t = torch.tensor([c.span_end()], dtype=torch.float64, device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            res[leg] = per_rank * world * steps / (float(t.item()) * 1e-3)
+        for kk in w.owned:
+            w.records("e2e", kk)           # raises if a count exceeded the staging capacity
+        bpp = sum(algorithmic_bytes_per_px(n).values())
+        halo = sorted({k for ids_ in w.shard.recv.values() for k in ids_})
+        out[name] = {"camera": cam, "keyframes_total": per_rank * world, "keyframes_per_rank": per_rank, "halo_keyframes_rank0": len(halo),
+                     "neighbours": n, "prior_sigmas": sig, "steps": steps, "warmup": 1, "scaling": scaling, "n_gpus": world,
+                     "value": res["value"], "e2e": res["e2e"], "unit": UNIT,
+                     "whole_path_frac_per_gpu": bpp * w.W * w.H * res["value"] / world / 1e9 / peak}
+        if name.startswith("config3") and not args.no_seam_check:
+            a3 = argparse.Namespace(**dict(vars(args), prior_sigmas=sig))
+            pick = lambda r, seam: ([seam[-1]] if r == 0 else [seam[0]]) if r < 2 and seam else []
+            out[name]["seam_parity"] = seam_parity(a3, torch, dist, dev, pkg, synth, w, world, rank, only=pick,
+                                                   threads=max(1, host_cores() // 2))
+        w = None
+        c.comm_destroy()
+        c.close()
+        dist.barrier()
+    return out
 
 
 def write_class_scene(path, synth, wl, n):
