@@ -633,7 +633,8 @@ constexpr int K1_WARP_SMEM = 512 + 256 + 4 * K1_QCAP + 4 * 128 + 16;  // 3 472 b
 //  (B) per lane: walk the line run by run (a run = consecutive columns on one image row, clipped to
 //      a 32-column word of the bit plane): ONE u32 load yields every column of the run that passes
 //      condition 1 and can pass condition 3.  Selected columns are appended to a per-warp queue
-//      (positions from a warp prefix sum: no atomics).
+//      (K1_ATOMIC_QUEUE 1, the default: each lane takes its positions with one shared-memory atomicAdd, the warp total
+//      comes from a REDUX; 0: positions from a five-step shuffle prefix sum, no atomics).
 //  (C) whenever 32 are queued they are evaluated one per lane, whichever lane they came from: exact
 //      conditions 2+3 on GradTheta, photometric + gradient residual (PM.cc:433-436) with the err
 //      of PM.cc:436 in float; a shared-memory atomicMin keeps the smallest err per owner, attempted
