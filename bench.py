@@ -616,7 +616,10 @@ def run_b200(args):
             wi = float(prof["warp_instructions_per_keyframe"])
             slots = 148 * 4 * sm_mhz * 1e6 * (1.0 / (value / world))
             issue = {"bound": "issue", "warp_instructions_per_keyframe": wi, "issue_slots_per_keyframe": slots,
-                     "frac": wi / slots, "sm_mhz": sm_mhz, "source": prof.get("warp_instructions_source")}
+                     "frac": wi / slots, "sm_mhz": sm_mhz, "source": prof.get("warp_instructions_source"),
+                     "note": "instruction count = AVERAGE over the key frames of the ncu launch list (k1_search 155 M per launch); the "
+                             "single --set full capture of one k1_search launch (profiles/*_k1_search_ncu_full.json, 134.7 M) is one "
+                             "key frame early in the sequence and is not what this fraction uses"}
 
         def e2e_entry(leg):
             h2d, d2h = bytes_ps[leg]
